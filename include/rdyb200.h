@@ -1,0 +1,192 @@
+/* rdyb200.h — C-ABI of the B200-native shallow-water (SWE) right-hand-side path.
+ *
+ * Drop-in boundary for RDycore's PETSc operator backend.  Every entry point
+ * is `extern "C"`, takes plain pointers and sizes, returns an int error code
+ * (0 = success, like PetscErrorCode) and never exits the process.  The last
+ * error text of the calling thread is available from rdyb_last_error().
+ *
+ * Citations are relative to the RDycore source tree (reference):
+ *   Operator / PetscOperator ABI      include/private/rdyoperatorimpl.h:75-90,107-213
+ *   flux factories                    src/operator_fluxes_petsc.c:17-95
+ *   source factories                  src/operator_sources_petsc.c:13-45
+ *   CPU kernels replaced              src/swe/swe_petsc.c, src/swe/swe_roe_flux_petsc.h
+ *   RHS callback + TS stage update    src/rdysetup.c:1120-1172, 1183-1196
+ *   mesh quantities consumed          include/private/rdymeshimpl.h:26-75,106-140
+ *   data access                       src/operator.c:1045-1086,1203-1290,1394-1464
+ *   diagnostics                       src/operator.c:757-768,867-893
+ */
+#ifndef RDYB200_H
+#define RDYB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error codes (values of the PETSc codes the reference raises) ---- */
+#define RDYB_SUCCESS 0
+#define RDYB_ERR_MEM 55      /* PETSC_ERR_MEM */
+#define RDYB_ERR_SUP 56      /* PETSC_ERR_SUP: unsupported configuration */
+#define RDYB_ERR_ARG_SIZ 60  /* PETSC_ERR_ARG_SIZ */
+#define RDYB_ERR_ARG 62      /* PETSC_ERR_ARG_WRONG */
+#define RDYB_ERR_USER 83     /* PETSC_ERR_USER: what PetscCheck(..., PETSC_ERR_USER, ...) raises */
+#define RDYB_ERR_CUDA 97     /* PETSC_ERR_GPU */
+#define RDYB_ERR_NCCL 98
+
+/* ---- enums: same numeric values as the reference ---- */
+/* include/rdycore.h:133-139 (RDyConditionType) */
+enum { RDYB_CONDITION_DIRICHLET = 0, RDYB_CONDITION_NEUMANN = 1, RDYB_CONDITION_REFLECTING = 2, RDYB_CONDITION_CRITICAL_OUTFLOW = 3 };
+/* include/private/rdyconfigimpl.h:52-56 (RDyFlowSourceMethod) */
+enum { RDYB_SOURCE_SEMI_IMPLICIT = 0, RDYB_SOURCE_IMPLICIT_XQ2018 = 1 };
+/* include/private/rdyconfigimpl.h:58-62 (RDyWellBalanceMethod); BS2002 falls back to NONE in the PETSc backend (src/operator.c:202-209) */
+enum { RDYB_WELL_BALANCING_NONE = 0, RDYB_WELL_BALANCING_BS2002 = 1, RDYB_WELL_BALANCING_HR = 2 };
+/* include/private/rdyconfigimpl.h:110-115 (RDyNumericsTemporal) */
+enum { RDYB_TEMPORAL_EULER = 0, RDYB_TEMPORAL_RK4 = 1 };
+
+/* Physics / numerics parameters the kernels read.  Filled from RDyConfig:
+ * config.physics.flow.{tiny_h,h_anuga_regular,source.method,source.xq2018_threshold,well_balancing},
+ * config.numerics.temporal.  Defaults: src/yaml_input.c:854-865. */
+typedef struct {
+  double  tiny_h;           /* default 1e-7 */
+  double  h_anuga_regular;  /* default 0.0 */
+  double  xq2018_threshold; /* default 1e-10 */
+  int32_t source_method;    /* RDYB_SOURCE_* */
+  int32_t well_balancing;   /* RDYB_WELL_BALANCING_* */
+  int32_t temporal;         /* RDYB_TEMPORAL_* */
+  int32_t reserved;
+} RdybConfig;
+
+/* A borrowed, read-only view of the RDyMesh arrays the path consumes
+ * (include/private/rdymeshimpl.h).  Local numbering, PetscInt = int32.
+ * A maintainer fills it with pointer assignments from RDyMesh; nothing is
+ * retained after rdyb_operator_create() returns. */
+typedef struct {
+  int32_t num_cells;           /* RDyMesh.num_cells (owned + ghost) */
+  int32_t num_owned_cells;     /* RDyMesh.num_owned_cells */
+  int32_t num_edges;           /* RDyMesh.num_edges */
+  int32_t num_internal_edges;  /* RDyMesh.num_internal_edges */
+  /* cells, length num_cells */
+  const int32_t *cell_is_owned;       /* RDyCells.is_owned */
+  const int32_t *cell_local_to_owned; /* RDyCells.local_to_owned */
+  const int64_t *cell_global_ids;     /* RDyCells.global_ids (may be NULL => local id) */
+  const double  *cell_areas;          /* RDyCells.areas */
+  const double  *cell_dz_dx;          /* RDyCells.dz_dx */
+  const double  *cell_dz_dy;          /* RDyCells.dz_dy */
+  const double  *cell_zc;             /* HR bed elevation, swe_petsc.c:1208-1224 (NULL unless HR) */
+  const double  *cell_xc, *cell_yc;   /* RDyCells.centroids[].X[0..1]; used only to order cells for locality (may be NULL) */
+  /* edges, length num_edges unless noted */
+  const int32_t *edge_cell_ids;       /* RDyEdges.cell_ids, [2e] left, [2e+1] right or -1 */
+  const double  *edge_lengths;        /* RDyEdges.lengths */
+  const double  *edge_cn, *edge_sn;   /* RDyEdges.cn, sn */
+  const int32_t *internal_edge_ids;   /* RDyEdges.internal_edge_ids, length num_internal_edges */
+  const int64_t *edge_global_ids;     /* RDyEdges.global_ids (may be NULL => local id) */
+} RdybMeshView;
+
+/* One RDyBoundary (include/private/rdyboundaryimpl.h:9-16) with the flow
+ * type of its RDyCondition (include/private/rdyconditionimpl.h:12-24). */
+typedef struct {
+  int32_t        id, index;
+  int32_t        num_edges;
+  const int32_t *edge_ids; /* local edge ids */
+  int32_t        bc_type;  /* RDYB_CONDITION_* */
+} RdybBoundaryView;
+
+/* CourantNumberDiagnostics, include/private/rdyoperatorimpl.h:21-25 */
+typedef struct {
+  double  max_courant_num;
+  int64_t global_edge_id;
+  int64_t global_cell_id;
+} RdybCourantDiagnostics;
+
+/* Halo plan for one rank: which owned cells go to which peer and which ghost
+ * cells arrive from which peer (cell ids are LOCAL ids of the RdybMeshView).
+ * Replaces the PetscSF behind DMGlobalToLocal (src/rdysetup.c:1133-1134). */
+typedef struct {
+  int32_t        num_peers;
+  const int32_t *peer_ranks;   /* [num_peers] */
+  const int32_t *send_offsets; /* [num_peers+1] into send_cells */
+  const int32_t *send_cells;   /* local ids of owned cells, per peer, ascending global id */
+  const int32_t *recv_offsets; /* [num_peers+1] into recv_cells */
+  const int32_t *recv_cells;   /* local ids of ghost cells, per peer, ascending global id */
+} RdybHaloView;
+
+typedef struct RdybOperator_ *RdybOperator;
+
+const char *rdyb_last_error(void);
+int         rdyb_version(int *major, int *minor);
+/* number of kernels this library launched on the calling process since load */
+int64_t rdyb_kernel_launch_count(void);
+
+/* ---- construction: CreateOperator (src/operator.c:348-417) for the SWE/PETSc case ----
+ * `device` = CUDA ordinal.  `cuda_stream` = a cudaStream_t to enqueue on (NULL => a stream the operator owns). */
+int rdyb_operator_create(const RdybConfig *config, const RdybMeshView *mesh, int32_t num_boundaries, const RdybBoundaryView *boundaries,
+                         const RdybHaloView *halo /* NULL for serial */, int device, void *cuda_stream, RdybOperator *op);
+int rdyb_operator_destroy(RdybOperator *op);
+int rdyb_operator_num_owned_cells(RdybOperator op, int32_t *n);
+int rdyb_operator_num_local_cells(RdybOperator op, int32_t *n);
+/* toggles: Courant diagnostics every apply (reference always does, swe_petsc.c:289-296), flux-divergence /
+ * primitive-variable outputs (src/operator.c:224-299), boundary flux accumulation (swe_petsc.c:623) */
+int rdyb_operator_set_options(RdybOperator op, int courant, int flux_divergence, int primitive_variables, int boundary_fluxes);
+
+/* ---- operator data (host arrays in the reference's layouts) ---- */
+/* SetOperatorBoundaryValues, src/operator.c:1045-1061: values[num_comp*e + c] -> components [comp_offset, comp_offset+num_comp) */
+int rdyb_operator_set_boundary_values(RdybOperator op, int32_t boundary_index, int32_t comp_offset, int32_t num_comp, int32_t num_edges,
+                                      const double *values);
+/* ExtractOperatorBoundaryFluxes, src/operator.c:1069-1086: accumulated fluxes, values[c][e] flattened as c*num_edges+e */
+int rdyb_operator_get_boundary_fluxes(RdybOperator op, int32_t boundary_index, int32_t num_edges, int accumulated, double *values);
+/* Get/RestoreOperatorDomainExternalSource, src/operator.c:1394-1429: one component, owned order */
+int rdyb_operator_set_external_source(RdybOperator op, int32_t component, int32_t num_owned, const double *values);
+int rdyb_operator_get_external_source(RdybOperator op, int32_t component, int32_t num_owned, double *values);
+/* Get/RestoreOperatorRegionalExternalSource, src/operator.c:1203-1241: values[i] -> owned cell owned_cell_ids[i] */
+int rdyb_operator_set_regional_external_source(RdybOperator op, int32_t component, int32_t n, const int32_t *owned_cell_ids, const double *values);
+/* Get/RestoreOperatorDomainMaterialProperties (Manning's n), src/operator.c:1435-1464 */
+int rdyb_operator_set_mannings(RdybOperator op, int32_t num_owned, const double *values);
+int rdyb_operator_set_regional_mannings(RdybOperator op, int32_t n, const int32_t *owned_cell_ids, const double *values);
+
+/* ---- state: the solution Vec (AoS [h,hu,hv], block size 3) ---- */
+/* u_global: owned order, 3*num_owned doubles (rdy->u_global, src/rdydm.c:254-292) */
+int rdyb_operator_set_state(RdybOperator op, const double *u_global);
+int rdyb_operator_get_state(RdybOperator op, double *u_global);
+/* RDyGetOwnedCell{Heights,XMomenta,YMomenta}, src/rdydata.c: one component, owned order */
+int rdyb_operator_get_state_component(RdybOperator op, int32_t component, int32_t num_owned, double *values);
+
+/* ---- the hot path ---- */
+/* PetscOperator apply shape (include/private/rdyoperatorimpl.h:80) with HOST arrays:
+ * u_local = AoS [num_cells][3] in the mesh view's local order (ghosts filled by the caller),
+ * f_global = AoS [num_owned][3]; computes flux + source exactly as ApplyPetscOperator
+ * (src/operator.c:656-672) after VecZeroEntries(F) (src/rdysetup.c:1130).  Copies in, runs, copies out. */
+int rdyb_operator_apply_host(RdybOperator op, double dt, const double *u_local, double *f_global);
+/* Same, on the device-resident state (ghosts refreshed by the halo exchange when a halo plan exists);
+ * F stays on the device; f_global may be NULL or a host array to download into. */
+int rdyb_operator_apply(RdybOperator op, double dt, double *f_global);
+/* OperatorRHSFunction + TSEULER step fused, nsteps times: U <- U + dt*F(U).  Asynchronous; state stays resident. */
+int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nsteps);
+/* classical RK4 (TSRK4) built from the RHS-only kernel and AXPY stage kernels */
+int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps);
+int rdyb_operator_synchronize(RdybOperator op);
+
+/* ---- diagnostics: Reset/Update/GetOperatorDiagnostics, src/operator.c:757-768,867-893 ---- */
+int rdyb_operator_reset_diagnostics(RdybOperator op);
+int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics *diags); /* local max since reset (syncs) */
+/* sum over owned cells of area*h (mass); deterministic two-stage reduction (syncs) */
+int rdyb_operator_get_mass(RdybOperator op, double *mass);
+
+/* ---- multi-GPU: NCCL communicator for the halo exchange ---- */
+int rdyb_nccl_unique_id(void *id128 /* 128 bytes out */);
+int rdyb_operator_init_comm(RdybOperator op, int32_t nranks, int32_t rank, const void *id128);
+/* run one halo exchange now (owned -> peers' ghosts) on the current state */
+int rdyb_operator_halo_exchange(RdybOperator op);
+
+/* ---- raw device pointers (for zero-copy binding to VECCUDA / torch tensors) ---- */
+/* which: 0..2 = h,hu,hv current state (length num_local), 3..5 = F (length num_owned) */
+int rdyb_operator_device_pointer(RdybOperator op, int32_t which, void **ptr, int64_t *length);
+/* timing helper: average kernel time of the last step_euler call's main kernel, measured with
+ * CUDA events on the operator's stream (ms per launch) */
+int rdyb_operator_last_kernel_ms(RdybOperator op, double *ms_per_launch, int32_t *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RDYB200_H */
