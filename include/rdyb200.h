@@ -130,6 +130,9 @@ int rdyb_operator_num_local_cells(RdybOperator op, int32_t *n);
  * primitive-variable outputs (src/operator.c:224-299), boundary flux accumulation (swe_petsc.c:623) */
 int rdyb_operator_set_options(RdybOperator op, int courant, int flux_divergence, int primitive_variables, int boundary_fluxes);
 
+/* kernel selection: kind 0 = K1 cell-centric gather (default), 1 = K2 shared-memory tiles of `tile_cells` cells */
+int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells);
+
 /* ---- operator data (host arrays in the reference's layouts) ---- */
 /* SetOperatorBoundaryValues, src/operator.c:1045-1061: values[num_comp*e + c] -> components [comp_offset, comp_offset+num_comp) */
 int rdyb_operator_set_boundary_values(RdybOperator op, int32_t boundary_index, int32_t comp_offset, int32_t num_comp, int32_t num_edges,
@@ -151,6 +154,13 @@ int rdyb_operator_set_state(RdybOperator op, const double *u_global);
 int rdyb_operator_get_state(RdybOperator op, double *u_global);
 /* RDyGetOwnedCell{Heights,XMomenta,YMomenta}, src/rdydata.c: one component, owned order */
 int rdyb_operator_get_state_component(RdybOperator op, int32_t component, int32_t num_owned, double *values);
+
+/* optional output Vecs of the last apply in the reference's AoS owned layout (3*num_owned doubles):
+ * which = 0 flux_divergence ("riemannf", src/operator.c:224-260), 1 primitive_variables (:264-299), 2 F */
+int rdyb_operator_get_field(RdybOperator op, int32_t which, double *values);
+/* pinned host memory for host-Vec callers of rdyb_operator_apply_host */
+int rdyb_host_alloc(size_t bytes, void **ptr);
+int rdyb_host_free(void *ptr);
 
 /* ---- the hot path ---- */
 /* PetscOperator apply shape (include/private/rdyoperatorimpl.h:80) with HOST arrays:

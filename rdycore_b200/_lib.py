@@ -92,7 +92,8 @@ OPERATOR_SYMBOLS = [
     "rdyb_operator_get_state_component", "rdyb_operator_apply_host", "rdyb_operator_apply", "rdyb_operator_step_euler",
     "rdyb_operator_step_rk4", "rdyb_operator_synchronize", "rdyb_operator_reset_diagnostics", "rdyb_operator_get_courant",
     "rdyb_operator_get_mass", "rdyb_nccl_unique_id", "rdyb_operator_init_comm", "rdyb_operator_halo_exchange",
-    "rdyb_operator_device_pointer", "rdyb_operator_last_kernel_ms",
+    "rdyb_operator_device_pointer", "rdyb_operator_last_kernel_ms", "rdyb_operator_set_kernel", "rdyb_operator_get_field",
+    "rdyb_host_alloc", "rdyb_host_free",
 ]
 
 _lib = None

@@ -16,11 +16,11 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librdyb200.so")
 OBJDIR = os.path.join(HERE, "build")
 
-C_SOURCES = ["rdyb_error.c", "host_mesh.c", "device_layout.c", "rdy_driver.c"]
+C_SOURCES = ["rdyb_error.c", "host_mesh.c", "device_layout.c", "petsc_operator_b200.c", "rdy_driver.c"]
 CU_SOURCES = ["swe_device.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC", "--use_fast_math=false" if False else "-Xptxas", "-v",
+    "-Xcompiler", "-fPIC", "-Xptxas", "-v", "-Wno-deprecated-gpu-targets",
 ]
 
 
@@ -72,7 +72,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
             _run([nvcc, *NVCC_FLAGS, *inc, "-c", src, "-o", obj], log)
         objs.append(obj)
     if force or _newer(objs, LIB):
-        _run([nvcc, "-shared", "-o", LIB, *objs, "-lm", "-ldl"], log)
+        _run([nvcc, "-shared", "-Wno-deprecated-gpu-targets", "-o", LIB, *objs, "-lm", "-ldl"], log)
     if verbose:
         print("\n".join(log))
     with open(os.path.join(OBJDIR, "build.log"), "a") as f:
@@ -80,9 +80,23 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def _all_sources() -> list[str]:
+    out = [os.path.join(ROOT, "include", h) for h in os.listdir(os.path.join(ROOT, "include"))]
+    out += [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
+    return out
+
+
+def stale() -> bool:
+    """True when a source file is newer than the built library."""
+    return _newer(_all_sources(), LIB)
+
+
 def build_oracles() -> None:
     """Build the CPU oracles (test infrastructure): the port always, oracle/_ref where the reference tree exists."""
-    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port", "ref"], check=True, capture_output=True)
+    p = subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port", "ref"], capture_output=True, text=True)
+    if p.returncode != 0:
+        sys.stderr.write(p.stdout + p.stderr)
+        raise RuntimeError("building the CPU oracles failed")
 
 
 if __name__ == "__main__":

@@ -93,3 +93,61 @@ def dam_break_quads(nx=100, ny=100, lx=10.0, ly=5.0, source_method=IMPLICIT_XQ20
     u0 = np.zeros((n, 3))
     u0[:, 0] = np.where(xc < 0.5 * lx, 10.0, 5.0)
     return Case("dam_break_quads_%dx%d" % (nx, ny), mesh, make_config(source_method=source_method), bnd, u0, np.full(n, 0.015), None, dt)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# synthetic floodplain (configs C, D, E of BASELINE.json)
+# ---------------------------------------------------------------------------------------------------------------
+def _hash01(ids: np.ndarray, seed: int) -> np.ndarray:
+    """Deterministic U(0,1) per 64-bit id (splitmix64 finaliser) — independent of the partition a cell lands in."""
+    x = (ids.astype(np.uint64) + np.uint64(seed)) * np.uint64(0x9E3779B97F4A7C15)
+    x ^= x >> np.uint64(30)
+    x *= np.uint64(0xBF58476D1CE4E5B9)
+    x ^= x >> np.uint64(27)
+    x *= np.uint64(0x94D049BB133111EB)
+    x ^= x >> np.uint64(31)
+    return (x >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def floodplain(nx=2236, ny=2236, dx=10.0, eta0=18.0, hr=False, px=1, py=1, rank=0, source_method=SEMI_IMPLICIT, dt=None, zamp=None,
+               dam_column=None) -> Case:
+    """Config C (hr=False) / D (hr=True): nx x ny quads split into triangles along alternating diagonals, jittered vertices,
+    bathymetry z = 20 x/L + 5 zamp sin(2 pi x/3km) cos(2 pi y/2km) + 2 U(0,1), Manning n ~ U(0.02,0.06), rain
+    1e-5 (1+sin(2 pi x/5km)) (1+cos(2 pi y/5km)) m/s, lake at rest eta0, reflecting walls.  With px*py > 1 this is rank's
+    block of a px x py decomposition with one layer of face-neighbour ghosts and its halo plan."""
+    lx, ly = nx * dx, ny * dx
+    if zamp is None:
+        zamp = 1.5 if hr else 1.0
+    mesh = HostMesh.floodplain(nx, ny, lx, ly, jitter=0.2, zamp=zamp, seed=12345, px=px, py=py, rank=rank)
+    if hr:
+        mesh.override_2d_projection()
+        mesh.set_zc(None)
+    n_own = mesh.num_owned_cells
+    o2l = mesh.array("owned_to_local")
+    gids = mesh.array("cell_global_ids")[o2l]
+    xc, yc, zc = mesh.array("cell_xc")[o2l], mesh.array("cell_yc")[o2l], mesh.array("cell_zcen")[o2l]
+    if hr:
+        zc = mesh.view_arrays()["cell_zc"][o2l]
+    mann = 0.02 + 0.04 * _hash01(gids, 34567)
+    src = np.zeros((n_own, 3))
+    src[:, 0] = 1e-5 * (1.0 + np.sin(2 * np.pi * xc / 5000.0)) * (1.0 + np.cos(2 * np.pi * yc / 5000.0))
+    u0 = np.zeros((n_own, 3))
+    u0[:, 0] = np.maximum(0.0, eta0 - zc)
+    if dam_column is not None:
+        # a water column in the low corner drives wet/dry fronts (config D)
+        r, height = dam_column
+        u0[:, 0] = np.where((xc < r) & (yc < r), np.maximum(u0[:, 0], height - zc), u0[:, 0])
+        u0[:, 0] = np.maximum(u0[:, 0], 0.0)
+    bnd = boundaries_from_predicates(mesh, [])
+    # keep only boundary edges whose left cell is owned (the reference builds boundaries per rank the same way)
+    if px * py > 1:
+        va = mesh.view_arrays()
+        for b in bnd:
+            left = va["edge_cell_ids"][b.edge_ids, 0]
+            b.edge_ids = b.edge_ids[va["cell_is_owned"][left] == 1]
+    if dt is None:
+        hmax = max(float(u0[:, 0].max()), 1.0)
+        dt = 0.25 * 0.2 * dx / np.sqrt(GRAVITY * hmax)  # Courant ~ amax*L/A*dt with L/A ~ 0.3/dx*10
+    cfg = make_config(source_method=source_method, well_balancing=WB_HR if hr else WB_NONE)
+    return Case("floodplain_%s_%dx%dx2" % ("hr" if hr else "roe", nx, ny), mesh, cfg, bnd, u0, mann, src, float(dt),
+                info={"px": px, "py": py, "rank": rank, "eta0": eta0, "dx": dx})

@@ -1,0 +1,721 @@
+/* swe_device.cu — the thin C-ABI CUDA layer of the B200 SWE path (include/rdyb200.h).
+ *
+ * Owns device memory, streams, the NCCL communicator of the halo exchange and the kernel launches.  The host
+ * logic above it (mesh, device layout, RDy lifecycle) is C.  There is no CPU fallback: every entry point that
+ * computes needs a CUDA device and fails with RDYB_ERR_CUDA otherwise.
+ */
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <atomic>
+#include <vector>
+
+#include "device_layout.h"
+#include "rdyb200.h"
+#include "rdyb_error.h"
+#include "swe_kernels.cuh"
+#include "swe_tiled.cuh"
+
+static std::atomic<int64_t> g_launches{0};
+
+#define CU(call)                                                                                                   \
+  do {                                                                                                             \
+    cudaError_t e_ = (call);                                                                                       \
+    if (e_ != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "CUDA error %s at %s:%d (%s)", cudaGetErrorName(e_), __FILE__, __LINE__, cudaGetErrorString(e_)); \
+  } while (0)
+#define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
+
+/* ---------------- NCCL, bound at run time so that the library loads on hosts without it ---------------- */
+struct NcclApi {
+  void *handle = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+
+static int nccl_load() {
+  if (g_nccl.handle) return RDYB_SUCCESS;
+  const char *names[] = {"libnccl.so.2", "libnccl.so"};
+  void *h = nullptr;
+  for (const char *n : names) {
+    h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (h) break;
+  }
+  if (!h) return rdyb_fail(RDYB_ERR_NCCL, "NCCL library not found (%s)", dlerror());
+#define SYM(field, name)                                                                           \
+  do {                                                                                             \
+    *(void **)(&g_nccl.field) = dlsym(h, name);                                                    \
+    if (!g_nccl.field) return rdyb_fail(RDYB_ERR_NCCL, "NCCL symbol %s not found", name);           \
+  } while (0)
+  SYM(GetUniqueId, "ncclGetUniqueId"); SYM(CommInitRank, "ncclCommInitRank"); SYM(CommDestroy, "ncclCommDestroy");
+  SYM(GroupStart, "ncclGroupStart"); SYM(GroupEnd, "ncclGroupEnd"); SYM(Send, "ncclSend"); SYM(Recv, "ncclRecv");
+  SYM(AllReduce, "ncclAllReduce"); SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+  g_nccl.handle = h;
+  return RDYB_SUCCESS;
+}
+#define NC(call)                                                                                                   \
+  do {                                                                                                             \
+    ncclResult_t r_ = (call);                                                                                      \
+    if (r_ != ncclSuccess) return rdyb_fail(RDYB_ERR_NCCL, "NCCL error at %s:%d (%s)", __FILE__, __LINE__, g_nccl.GetErrorString(r_)); \
+  } while (0)
+
+/* ---------------- the operator ---------------- */
+struct RdybOperator_ {
+  RdybConfig cfg;
+  RdybLayout L;      /* host copy of the layout (index maps are needed by the setters) */
+  RdybTiledLayout T; /* tiled layout (host copy of the sizes; arrays are uploaded) */
+  int device = 0;
+  cudaStream_t stream = nullptr, comm_stream = nullptr;
+  bool own_stream = false;
+  cudaEvent_t ev_pack = nullptr, ev_halo = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+  int32_t N = 0, NL = 0, NI = 0, stride = 0, width = 0, nbe = 0;
+  /* device arrays */
+  double *state[2] = {nullptr, nullptr}; /* [3][stride] each; `cur` is the solution */
+  int cur = 0;
+  double *F = nullptr, *src = nullptr, *mann = nullptr, *fdiv = nullptr, *prim = nullptr;
+  double *inv_area = nullptr, *area = nullptr, *dzdx = nullptr, *dzdy = nullptr, *zc = nullptr;
+  int32_t *ell_nbr = nullptr;
+  double *ell_sn = nullptr, *ell_cn = nullptr, *ell_slen = nullptr;
+  int32_t *btype = nullptr;
+  double *bval = nullptr, *bflux = nullptr, *bacc = nullptr;
+  int32_t *dev_to_local = nullptr, *dev_to_owned = nullptr, *send_cells = nullptr;
+  double *stage = nullptr;    /* [3][stride] staging for host <-> device conversions */
+  int32_t *stage_idx = nullptr;
+  double *sendbuf = nullptr, *recvbuf = nullptr;
+  double *cmax = nullptr;
+  long long *carg = nullptr;
+  int32_t ncblocks = 0, ncblocks_interior = 0;
+  double *partial = nullptr;
+  double *rk_k[4] = {nullptr, nullptr, nullptr, nullptr}, *rk_y = nullptr;
+  /* tiled-kernel device arrays */
+  TiledDev td;
+  bool has_tiled = false;
+  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2) */
+  /* options */
+  bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
+  bool mom_src = false; /* any momentum external source set */
+  /* comm */
+  ncclComm_t comm = nullptr;
+  int32_t nranks = 1, rank = 0;
+  /* timing of the last step_euler call */
+  double last_ms = 0.0;
+  int32_t last_launches = 0;
+};
+
+template <typename T>
+static int dalloc(T **p, size_t n) {
+  CU(cudaMalloc((void **)p, sizeof(T) * (n > 0 ? n : 1)));
+  CU(cudaMemset(*p, 0, sizeof(T) * (n > 0 ? n : 1)));
+  return RDYB_SUCCESS;
+}
+template <typename T>
+static int upload(T **p, const T *src, size_t n) {
+  RDYB_CALL(dalloc(p, n));
+  if (n) CU(cudaMemcpy(*p, src, sizeof(T) * n, cudaMemcpyHostToDevice));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int64_t rdyb_kernel_launch_count(void) { return g_launches.load(); }
+
+static int grid_for(int64_t n, int block) { return (int)((n + block - 1) / block); }
+
+extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
+  if (!pop || !*pop) return RDYB_SUCCESS;
+  RdybOperator op = *pop;
+  cudaSetDevice(op->device);
+  if (op->stream) cudaStreamSynchronize(op->stream);
+  if (op->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(op->comm);
+  void *ptrs[] = {op->state[0], op->state[1], op->F, op->src, op->mann, op->fdiv, op->prim, op->inv_area, op->area, op->dzdx, op->dzdy, op->zc,
+                  op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
+                  op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
+                  op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  tiled_dev_free(&op->td);
+  if (op->ev_pack) cudaEventDestroy(op->ev_pack);
+  if (op->ev_halo) cudaEventDestroy(op->ev_halo);
+  if (op->ev_t0) cudaEventDestroy(op->ev_t0);
+  if (op->ev_t1) cudaEventDestroy(op->ev_t1);
+  if (op->comm_stream) cudaStreamDestroy(op->comm_stream);
+  if (op->own_stream && op->stream) cudaStreamDestroy(op->stream);
+  rdyb_layout_free(&op->L);
+  rdyb_tiled_layout_free(&op->T);
+  delete op;
+  *pop = nullptr;
+  return RDYB_SUCCESS;
+}
+
+static int operator_create_impl(RdybOperator op, const RdybConfig *config, const RdybMeshView *mesh, int32_t nb, const RdybBoundaryView *bnd,
+                                const RdybHaloView *halo, int device, void *cuda_stream) {
+  op->cfg = *config;
+  op->device = device;
+  RDYB_CHECK(config->source_method == RDYB_SOURCE_SEMI_IMPLICIT || config->source_method == RDYB_SOURCE_IMPLICIT_XQ2018, RDYB_ERR_USER,
+             "Only semi_implicit and implicit_xq2018 are supported in the PETSc version"); /* src/swe/swe_petsc.c:973-975 */
+  RDYB_CHECK(config->well_balancing != RDYB_WELL_BALANCING_HR || mesh->cell_zc, RDYB_ERR_USER, "hydrostatic reconstruction needs cell_zc");
+  for (int32_t b = 0; b < nb; ++b) {
+    const int t = bnd[b].bc_type;
+    RDYB_CHECK(t == RDYB_CONDITION_DIRICHLET || t == RDYB_CONDITION_REFLECTING || t == RDYB_CONDITION_CRITICAL_OUTFLOW, RDYB_ERR_USER,
+               "Invalid boundary condition encountered for boundary %d\n", bnd[b].id); /* src/swe/swe_petsc.c:567-569 */
+  }
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0)
+    return rdyb_fail(RDYB_ERR_CUDA, "no CUDA device available (%s): the SWE path has no CPU fallback", cudaGetErrorString(ce));
+  RDYB_CHECK(device >= 0 && device < ndev, RDYB_ERR_ARG, "device %d out of range (%d devices)", device, ndev);
+  CU(cudaSetDevice(device));
+  const char *no_reorder = getenv("RDYB_NO_REORDER");
+  RDYB_CALL(rdyb_layout_build(mesh, nb, bnd, halo, !(no_reorder && no_reorder[0] == '1'), &op->L));
+  const RdybLayout &L = op->L;
+  op->N = L.n_owned; op->NL = L.n_local; op->NI = L.n_interior; op->stride = L.stride; op->width = L.width; op->nbe = L.num_boundary_edges;
+  if (cuda_stream) op->stream = (cudaStream_t)cuda_stream;
+  else { CU(cudaStreamCreateWithFlags(&op->stream, cudaStreamNonBlocking)); op->own_stream = true; }
+  CU(cudaStreamCreateWithFlags(&op->comm_stream, cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&op->ev_pack, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&op->ev_halo, cudaEventDisableTiming));
+  CU(cudaEventCreate(&op->ev_t0));
+  CU(cudaEventCreate(&op->ev_t1));
+  const size_t S = (size_t)L.stride;
+  RDYB_CALL(dalloc(&op->state[0], 3 * S)); RDYB_CALL(dalloc(&op->state[1], 3 * S)); RDYB_CALL(dalloc(&op->F, 3 * S));
+  RDYB_CALL(dalloc(&op->src, 3 * S)); RDYB_CALL(dalloc(&op->mann, S)); RDYB_CALL(dalloc(&op->stage, 3 * S));
+  RDYB_CALL(dalloc(&op->stage_idx, S));
+  RDYB_CALL(upload(&op->inv_area, L.inv_area, S)); RDYB_CALL(upload(&op->area, L.area, S));
+  RDYB_CALL(upload(&op->dzdx, L.dzdx, S)); RDYB_CALL(upload(&op->dzdy, L.dzdy, S));
+  if (L.zc) RDYB_CALL(upload(&op->zc, L.zc, S));
+  const size_t W = (size_t)L.width * S;
+  RDYB_CALL(upload(&op->ell_nbr, L.ell_nbr, W)); RDYB_CALL(upload(&op->ell_sn, L.ell_sn, W));
+  RDYB_CALL(upload(&op->ell_cn, L.ell_cn, W)); RDYB_CALL(upload(&op->ell_slen, L.ell_slen, W));
+  RDYB_CALL(upload(&op->btype, L.b_type, (size_t)L.num_boundary_edges));
+  RDYB_CALL(dalloc(&op->bval, 3 * (size_t)L.num_boundary_edges)); RDYB_CALL(dalloc(&op->bflux, 3 * (size_t)L.num_boundary_edges));
+  RDYB_CALL(dalloc(&op->bacc, 3 * (size_t)L.num_boundary_edges));
+  RDYB_CALL(upload(&op->dev_to_local, L.dev_to_local, (size_t)L.n_local)); RDYB_CALL(upload(&op->dev_to_owned, L.dev_to_owned, (size_t)L.n_owned));
+  if (L.num_peers > 0) {
+    const size_t ns = (size_t)L.send_offsets[L.num_peers], nr = (size_t)L.recv_offsets[L.num_peers];
+    RDYB_CALL(upload(&op->send_cells, L.send_cells, ns));
+    RDYB_CALL(dalloc(&op->sendbuf, 3 * ns)); RDYB_CALL(dalloc(&op->recvbuf, 3 * nr));
+  }
+  op->ncblocks_interior = grid_for(op->NI, RDYB_BLOCK);
+  op->ncblocks = op->ncblocks_interior + grid_for(op->N - op->NI, RDYB_BLOCK) + 1;
+  /* the tiled kernel needs one slot per tile; tiles are never smaller than RDYB_BLOCK cells, so ncblocks covers both */
+  RDYB_CALL(dalloc(&op->cmax, (size_t)op->ncblocks)); RDYB_CALL(dalloc(&op->carg, (size_t)op->ncblocks));
+  CU(cudaMemset(op->carg, 0xff, sizeof(long long) * (size_t)op->ncblocks));
+  RDYB_CALL(dalloc(&op->partial, 1024));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_create(const RdybConfig *config, const RdybMeshView *mesh, int32_t nb, const RdybBoundaryView *bnd,
+                                    const RdybHaloView *halo, int device, void *cuda_stream, RdybOperator *out) {
+  RDYB_CHECK(config && mesh && out, RDYB_ERR_ARG, "rdyb_operator_create: NULL argument");
+  RDYB_CHECK(nb >= 0 && (nb == 0 || bnd), RDYB_ERR_ARG, "rdyb_operator_create: %d boundaries but no boundary array", nb);
+  RdybOperator op = new RdybOperator_();
+  memset(&op->L, 0, sizeof(op->L));
+  memset(&op->T, 0, sizeof(op->T));
+  memset(&op->td, 0, sizeof(op->td));
+  int ierr = operator_create_impl(op, config, mesh, nb, bnd, halo, device, cuda_stream);
+  if (ierr) {
+    char saved[1024];
+    snprintf(saved, sizeof(saved), "%s", rdyb_last_error());
+    rdyb_operator_destroy(&op);
+    return rdyb_fail(ierr, "%s", saved);
+  }
+  *out = op;
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_num_owned_cells(RdybOperator op, int32_t *n) {
+  RDYB_CHECK(op && n, RDYB_ERR_ARG, "NULL argument");
+  *n = op->N;
+  return RDYB_SUCCESS;
+}
+extern "C" int rdyb_operator_num_local_cells(RdybOperator op, int32_t *n) {
+  RDYB_CHECK(op && n, RDYB_ERR_ARG, "NULL argument");
+  *n = op->NL;
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_divergence, int primitive_variables, int boundary_fluxes) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  op->opt_courant = courant != 0; op->opt_fdiv = flux_divergence != 0; op->opt_prim = primitive_variables != 0; op->opt_bflux = boundary_fluxes != 0;
+  if (op->opt_fdiv && !op->fdiv) RDYB_CALL(dalloc(&op->fdiv, 3 * (size_t)op->stride));
+  if (op->opt_prim && !op->prim) RDYB_CALL(dalloc(&op->prim, 3 * (size_t)op->stride));
+  return RDYB_SUCCESS;
+}
+
+/* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
+extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  RDYB_CHECK(kind == 0 || kind == 1, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
+  CU(cudaSetDevice(op->device));
+  if (kind == 1) {
+    if (op->has_tiled && op->T.tile_cells != tile_cells) {
+      tiled_dev_free(&op->td);
+      rdyb_tiled_layout_free(&op->T);
+      op->has_tiled = false;
+    }
+    if (!op->has_tiled) {
+      RDYB_CALL(rdyb_tiled_layout_build(&op->L, tile_cells, &op->T));
+      RDYB_CALL(tiled_dev_upload(&op->T, &op->L, &op->td));
+      op->has_tiled = true;
+    }
+  }
+  op->kernel_kind = kind;
+  return RDYB_SUCCESS;
+}
+
+/* ---------------- data setters / getters ---------------- */
+extern "C" int rdyb_operator_set_boundary_values(RdybOperator op, int32_t b, int32_t comp_offset, int32_t num_comp, int32_t num_edges,
+                                                 const double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(b >= 0 && b < op->L.num_boundaries, RDYB_ERR_USER, "Invalid boundary index: %d", b);
+  const int32_t ne = op->L.b_offsets[b + 1] - op->L.b_offsets[b];
+  /* src/operator.c:1050-1052 */
+  RDYB_CHECK(num_edges == ne, RDYB_ERR_USER, "Wrong number of boundary edges for boundary %d: %d (should be %d)", b, num_edges, ne);
+  RDYB_CHECK(comp_offset >= 0 && num_comp > 0 && comp_offset + num_comp <= 3, RDYB_ERR_USER, "Invalid component range [%d, %d)", comp_offset,
+             comp_offset + num_comp);
+  CU(cudaSetDevice(op->device));
+  std::vector<double> tmp((size_t)ne);
+  for (int32_t c = 0; c < num_comp; ++c) {
+    for (int32_t e = 0; e < ne; ++e) tmp[e] = values[(size_t)num_comp * e + c];
+    CU(cudaMemcpyAsync(op->bval + (size_t)(comp_offset + c) * op->nbe + op->L.b_offsets[b], tmp.data(), sizeof(double) * ne, cudaMemcpyHostToDevice,
+                       op->stream));
+    CU(cudaStreamSynchronize(op->stream));
+  }
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_get_boundary_fluxes(RdybOperator op, int32_t b, int32_t num_edges, int accumulated, double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(b >= 0 && b < op->L.num_boundaries, RDYB_ERR_USER, "Invalid boundary index: %d", b);
+  const int32_t ne = op->L.b_offsets[b + 1] - op->L.b_offsets[b];
+  RDYB_CHECK(num_edges == ne, RDYB_ERR_USER, "Wrong number of boundary edges for boundary %d: %d (should be %d)", b, num_edges, ne);
+  RDYB_CHECK(op->opt_bflux, RDYB_ERR_USER, "boundary fluxes are not being recorded (rdyb_operator_set_options)");
+  CU(cudaSetDevice(op->device));
+  const double *srcp = accumulated ? op->bacc : op->bflux;
+  for (int32_t c = 0; c < 3; ++c)
+    CU(cudaMemcpyAsync(values + (size_t)c * ne, srcp + (size_t)c * op->nbe + op->L.b_offsets[b], sizeof(double) * ne, cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+
+/* owned-order host array -> one device-order component array */
+static int upload_owned_component(RdybOperator op, const double *values, double *dst) {
+  CU(cudaMemcpyAsync(op->stage, values, sizeof(double) * op->N, cudaMemcpyHostToDevice, op->stream));
+  gather_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_owned, dst, op->N);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+static int download_owned_component(RdybOperator op, const double *srcp, double *values) {
+  scatter_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(srcp, op->dev_to_owned, op->stage, op->N);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * op->N, cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+/* values[i] -> dst[owned_to_dev[ids[i]]] */
+static int upload_regional(RdybOperator op, int32_t n, const int32_t *ids, const double *values, double *dst) {
+  std::vector<int32_t> idx((size_t)n);
+  for (int32_t i = 0; i < n; ++i) {
+    RDYB_CHECK(ids[i] >= 0 && ids[i] < op->N, RDYB_ERR_USER, "owned cell id %d out of range", ids[i]);
+    idx[i] = op->L.owned_to_dev[ids[i]];
+  }
+  RDYB_CHECK(n <= op->stride, RDYB_ERR_ARG_SIZ, "region has more cells (%d) than the mesh", n);
+  CU(cudaMemcpyAsync(op->stage, values, sizeof(double) * n, cudaMemcpyHostToDevice, op->stream));
+  CU(cudaMemcpyAsync(op->stage_idx, idx.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, op->stream));
+  scatter_kernel<<<grid_for(n, 256), 256, 0, op->stream>>>(op->stage, op->stage_idx, dst, n);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_set_external_source(RdybOperator op, int32_t component, int32_t num_owned, const double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(component >= 0 && component < 3, RDYB_ERR_USER, "Invalid source component: %d", component);
+  RDYB_CHECK(num_owned == op->N, RDYB_ERR_USER, "Wrong size (%d) for owned cell data (should be %d)", num_owned, op->N);
+  CU(cudaSetDevice(op->device));
+  if (component > 0) op->mom_src = true;
+  return upload_owned_component(op, values, op->src + (size_t)component * op->stride);
+}
+extern "C" int rdyb_operator_get_external_source(RdybOperator op, int32_t component, int32_t num_owned, double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(component >= 0 && component < 3, RDYB_ERR_USER, "Invalid source component: %d", component);
+  RDYB_CHECK(num_owned == op->N, RDYB_ERR_USER, "Wrong size (%d) for owned cell data (should be %d)", num_owned, op->N);
+  CU(cudaSetDevice(op->device));
+  return download_owned_component(op, op->src + (size_t)component * op->stride, values);
+}
+extern "C" int rdyb_operator_set_regional_external_source(RdybOperator op, int32_t component, int32_t n, const int32_t *ids, const double *values) {
+  RDYB_CHECK(op && (n == 0 || (ids && values)), RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(component >= 0 && component < 3, RDYB_ERR_USER, "Invalid source component: %d", component);
+  CU(cudaSetDevice(op->device));
+  if (component > 0) op->mom_src = true;
+  return n ? upload_regional(op, n, ids, values, op->src + (size_t)component * op->stride) : RDYB_SUCCESS;
+}
+extern "C" int rdyb_operator_set_mannings(RdybOperator op, int32_t num_owned, const double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(num_owned == op->N, RDYB_ERR_USER, "Wrong size (%d) for owned cell data (should be %d)", num_owned, op->N);
+  CU(cudaSetDevice(op->device));
+  return upload_owned_component(op, values, op->mann);
+}
+extern "C" int rdyb_operator_set_regional_mannings(RdybOperator op, int32_t n, const int32_t *ids, const double *values) {
+  RDYB_CHECK(op && (n == 0 || (ids && values)), RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  return n ? upload_regional(op, n, ids, values, op->mann) : RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_set_state(RdybOperator op, const double *u_global) {
+  RDYB_CHECK(op && u_global, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  CU(cudaMemcpyAsync(op->stage, u_global, sizeof(double) * 3 * op->N, cudaMemcpyHostToDevice, op->stream));
+  aos_to_soa_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_owned, op->state[op->cur], op->N, op->stride);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+extern "C" int rdyb_operator_get_state(RdybOperator op, double *u_global) {
+  RDYB_CHECK(op && u_global, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->state[op->cur], op->dev_to_owned, op->stage, op->N, op->stride);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(u_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+extern "C" int rdyb_operator_get_state_component(RdybOperator op, int32_t component, int32_t num_owned, double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(component >= 0 && component < 3, RDYB_ERR_USER, "Invalid component: %d", component);
+  RDYB_CHECK(num_owned == op->N, RDYB_ERR_USER, "Wrong size (%d) for owned cell data (should be %d)", num_owned, op->N);
+  CU(cudaSetDevice(op->device));
+  return download_owned_component(op, op->state[op->cur] + (size_t)component * op->stride, values);
+}
+/* optional output vectors in the reference's AoS owned layout: which = 0 flux_divergence, 1 primitive_variables, 2 F of the last apply */
+extern "C" int rdyb_operator_get_field(RdybOperator op, int32_t which, double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  const double *srcp = which == 0 ? op->fdiv : which == 1 ? op->prim : which == 2 ? op->F : nullptr;
+  RDYB_CHECK(srcp, RDYB_ERR_USER, "field %d is not being computed (rdyb_operator_set_options)", which);
+  CU(cudaSetDevice(op->device));
+  soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(srcp, op->dev_to_owned, op->stage, op->N, op->stride);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+
+/* ---------------- launches ---------------- */
+static void fill_args(RdybOperator op, SweArgs &a, const double *in, double *out, double dt) {
+  const size_t S = (size_t)op->stride;
+  a.h = in; a.hu = in + S; a.hv = in + 2 * S;
+  a.o0 = out; a.o1 = out + S; a.o2 = out + 2 * S;
+  a.inv_area = op->inv_area; a.dzdx = op->dzdx; a.dzdy = op->dzdy; a.zc = op->zc; a.mann = op->mann;
+  a.s0 = op->src; a.s1 = op->mom_src ? op->src + S : nullptr; a.s2 = op->mom_src ? op->src + 2 * S : nullptr;
+  a.nbr = op->ell_nbr; a.esn = op->ell_sn; a.ecn = op->ell_cn; a.eslen = op->ell_slen;
+  a.btype = op->btype; a.bval = op->bval;
+  a.bflux = op->opt_bflux ? op->bflux : nullptr; a.bacc = op->opt_bflux ? op->bacc : nullptr;
+  a.nbe = op->nbe;
+  a.fdiv = op->opt_fdiv ? op->fdiv : nullptr; a.prim = op->opt_prim ? op->prim : nullptr;
+  a.cmax = nullptr; a.carg = nullptr;
+  a.stride = op->stride; a.width = op->width; a.begin = 0; a.end = 0;
+  a.dt = dt; a.tiny_h = op->cfg.tiny_h; a.ha2 = op->cfg.h_anuga_regular * op->cfg.h_anuga_regular; a.xq_thr = op->cfg.xq2018_threshold;
+}
+
+template <bool HR, int SRC, bool EULER>
+static void launch_gather_c(RdybOperator op, const SweArgs &a, int grid) {
+  if (op->opt_courant) swe_gather_kernel<HR, SRC, EULER, true><<<grid, RDYB_BLOCK, 0, op->stream>>>(a);
+  else swe_gather_kernel<HR, SRC, EULER, false><<<grid, RDYB_BLOCK, 0, op->stream>>>(a);
+}
+template <bool EULER>
+static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
+  const bool hr = op->cfg.well_balancing == RDYB_WELL_BALANCING_HR;
+  const bool xq = op->cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
+  if (hr) { if (xq) launch_gather_c<true, 1, EULER>(op, a, grid); else launch_gather_c<true, 0, EULER>(op, a, grid); }
+  else { if (xq) launch_gather_c<false, 1, EULER>(op, a, grid); else launch_gather_c<false, 0, EULER>(op, a, grid); }
+}
+
+/* one RHS / Euler pass over owned device cells [begin,end) */
+static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
+  if (end <= begin) return RDYB_SUCCESS;
+  if (op->kernel_kind == 1 && op->has_tiled) {
+    RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, in, out, op->src, op->mom_src, op->mann, op->btype, op->bval, op->opt_bflux ? op->bflux : nullptr,
+                           op->opt_bflux ? op->bacc : nullptr, op->nbe, op->opt_fdiv ? op->fdiv : nullptr, op->opt_prim ? op->prim : nullptr,
+                           op->opt_courant ? op->cmax : nullptr, op->carg, dt, euler, begin, end, op->stream));
+    LAUNCHED();
+    CU(cudaGetLastError());
+    return RDYB_SUCCESS;
+  }
+  SweArgs a;
+  fill_args(op, a, in, out, dt);
+  a.begin = begin; a.end = end;
+  if (op->opt_courant) { a.cmax = op->cmax + cslot0; a.carg = op->carg + cslot0; }
+  const int grid = grid_for(end - begin, RDYB_BLOCK);
+  if (euler) launch_gather<true>(op, a, grid);
+  else launch_gather<false>(op, a, grid);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  return RDYB_SUCCESS;
+}
+
+/* ---------------- halo exchange ---------------- */
+static int halo_begin(RdybOperator op, double *state) {
+  const RdybLayout &L = op->L;
+  if (L.num_peers == 0 || !op->comm) return RDYB_SUCCESS;
+  const int32_t ns = L.send_offsets[L.num_peers], nr = L.recv_offsets[L.num_peers];
+  if (ns > 0) {
+    halo_pack_kernel<<<grid_for(ns, 256), 256, 0, op->stream>>>(state, op->send_cells, op->sendbuf, ns, op->stride);
+    LAUNCHED();
+    CU(cudaGetLastError());
+  }
+  CU(cudaEventRecord(op->ev_pack, op->stream));
+  CU(cudaStreamWaitEvent(op->comm_stream, op->ev_pack, 0));
+  NC(g_nccl.GroupStart());
+  for (int32_t p = 0; p < L.num_peers; ++p) {
+    const int32_t s0 = L.send_offsets[p], sn = L.send_offsets[p + 1] - s0, r0 = L.recv_offsets[p], rn = L.recv_offsets[p + 1] - r0;
+    for (int c = 0; c < 3; ++c) {
+      /* one message per component so that both ends can address plain [3][n] buffers */
+      if (sn > 0) NC(g_nccl.Send(op->sendbuf + (size_t)c * ns + s0, (size_t)sn, ncclDouble, L.peer_ranks[p], op->comm, op->comm_stream));
+      if (rn > 0) NC(g_nccl.Recv(op->recvbuf + (size_t)c * nr + r0, (size_t)rn, ncclDouble, L.peer_ranks[p], op->comm, op->comm_stream));
+    }
+  }
+  NC(g_nccl.GroupEnd());
+  if (nr > 0) {
+    halo_unpack_kernel<<<grid_for(nr, 256), 256, 0, op->comm_stream>>>(op->recvbuf, state, nr, op->N, op->stride);
+    LAUNCHED();
+    CU(cudaGetLastError());
+  }
+  CU(cudaEventRecord(op->ev_halo, op->comm_stream));
+  return RDYB_SUCCESS;
+}
+static int halo_end(RdybOperator op) {
+  if (op->L.num_peers == 0 || !op->comm) return RDYB_SUCCESS;
+  CU(cudaStreamWaitEvent(op->stream, op->ev_halo, 0));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_nccl_unique_id(void *id128) {
+  RDYB_CHECK(id128, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CALL(nccl_load());
+  ncclUniqueId id;
+  NC(g_nccl.GetUniqueId(&id));
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is expected to be 128 bytes");
+  memcpy(id128, &id, 128);
+  return RDYB_SUCCESS;
+}
+extern "C" int rdyb_operator_init_comm(RdybOperator op, int32_t nranks, int32_t rank, const void *id128) {
+  RDYB_CHECK(op && id128, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(nranks >= 1 && rank >= 0 && rank < nranks, RDYB_ERR_ARG, "bad rank %d of %d", rank, nranks);
+  RDYB_CALL(nccl_load());
+  CU(cudaSetDevice(op->device));
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  NC(g_nccl.CommInitRank(&op->comm, nranks, id, rank));
+  op->nranks = nranks; op->rank = rank;
+  return RDYB_SUCCESS;
+}
+extern "C" int rdyb_operator_halo_exchange(RdybOperator op) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  RDYB_CALL(halo_begin(op, op->state[op->cur]));
+  RDYB_CALL(halo_end(op));
+  return RDYB_SUCCESS;
+}
+
+/* one RHS (or fused Euler) evaluation of `in` into `out`, with the halo exchange of `in` overlapped with the interior cells */
+static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool euler) {
+  const bool exchange = op->L.num_peers > 0 && op->comm;
+  if (exchange) {
+    RDYB_CALL(halo_begin(op, in));
+    RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->NI, 0));
+    RDYB_CALL(halo_end(op));
+    RDYB_CALL(launch_cells(op, in, out, dt, euler, op->NI, op->N, op->ncblocks_interior));
+  } else {
+    if (op->NI > 0 && op->NI < op->N && op->kernel_kind == 0) {
+      /* serial with caller-filled ghosts: two ranges keep the Courant slots consistent with the exchange path */
+      RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->NI, 0));
+      RDYB_CALL(launch_cells(op, in, out, dt, euler, op->NI, op->N, op->ncblocks_interior));
+    } else {
+      RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->N, 0));
+    }
+  }
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double *u_local, double *f_global) {
+  RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  /* u_local (AoS, view order, ghosts included) -> device SoA */
+  CU(cudaMemcpyAsync(op->stage, u_local, sizeof(double) * 3 * op->NL, cudaMemcpyHostToDevice, op->stream));
+  aos_to_soa_kernel<<<grid_for(op->NL, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_local, op->state[op->cur], op->NL, op->stride);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  /* ghosts come from the caller here (DMGlobalToLocal already ran): no exchange */
+  ncclComm_t saved = op->comm;
+  op->comm = nullptr;
+  int ierr = rhs_pass(op, op->state[op->cur], op->F, dt, false);
+  op->comm = saved;
+  RDYB_CALL(ierr);
+  soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->F, op->dev_to_owned, op->stage, op->N, op->stride);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(f_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_apply(RdybOperator op, double dt, double *f_global) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  RDYB_CALL(rhs_pass(op, op->state[op->cur], op->F, dt, false));
+  if (f_global) {
+    soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->F, op->dev_to_owned, op->stage, op->N, op->stride);
+    LAUNCHED();
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(f_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
+    CU(cudaStreamSynchronize(op->stream));
+  }
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nsteps) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  RDYB_CHECK(nsteps >= 0, RDYB_ERR_ARG, "negative step count");
+  CU(cudaSetDevice(op->device));
+  CU(cudaEventRecord(op->ev_t0, op->stream));
+  for (int32_t s = 0; s < nsteps; ++s) {
+    RDYB_CALL(rhs_pass(op, op->state[op->cur], op->state[op->cur ^ 1], dt, true));
+    op->cur ^= 1;
+  }
+  CU(cudaEventRecord(op->ev_t1, op->stream));
+  op->last_launches = nsteps;
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  const size_t S = (size_t)op->stride;
+  for (int i = 0; i < 4; ++i)
+    if (!op->rk_k[i]) RDYB_CALL(dalloc(&op->rk_k[i], 3 * S));
+  if (!op->rk_y) RDYB_CALL(dalloc(&op->rk_y, 3 * S));
+  /* classical tableau, as PETSc TSRK4: Y_i = U + dt*a_i*K_{i-1}; U += dt*(K0/6 + K1/3 + K2/3 + K3/6) */
+  const double a[4] = {0.0, 0.5, 0.5, 1.0};
+  const double bw[4] = {1.0 / 6.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 6.0};
+  const int g = grid_for(op->N, 256);
+  for (int32_t s = 0; s < nsteps; ++s) {
+    double *U = op->state[op->cur];
+    for (int i = 0; i < 4; ++i) {
+      double *Y = U;
+      if (i > 0) {
+        stage_axpy_kernel<<<g, 256, 0, op->stream>>>(U, op->rk_k[i - 1], dt * a[i], op->rk_y, op->N, op->stride);
+        LAUNCHED();
+        CU(cudaGetLastError());
+        Y = op->rk_y;
+      }
+      RDYB_CALL(rhs_pass(op, Y, op->rk_k[i], dt, false));
+    }
+    rk4_combine_kernel<<<g, 256, 0, op->stream>>>(U, op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], dt * bw[0], dt * bw[1], dt * bw[2],
+                                                  dt * bw[3], op->N, op->stride);
+    LAUNCHED();
+    CU(cudaGetLastError());
+  }
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_synchronize(RdybOperator op) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  CU(cudaStreamSynchronize(op->comm_stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+
+/* ---------------- diagnostics ---------------- */
+extern "C" int rdyb_operator_reset_diagnostics(RdybOperator op) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  CU(cudaMemsetAsync(op->cmax, 0, sizeof(double) * (size_t)op->ncblocks, op->stream));
+  CU(cudaMemsetAsync(op->carg, 0xff, sizeof(long long) * (size_t)op->ncblocks, op->stream));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics *d) {
+  RDYB_CHECK(op && d, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  std::vector<double> v((size_t)op->ncblocks);
+  std::vector<long long> a((size_t)op->ncblocks);
+  CU(cudaMemcpyAsync(v.data(), op->cmax, sizeof(double) * v.size(), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaMemcpyAsync(a.data(), op->carg, sizeof(long long) * a.size(), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  d->max_courant_num = 0.0; d->global_edge_id = -1; d->global_cell_id = -1; /* ResetOperatorDiagnostics, src/operator.c:757-768 */
+  long long arg = -1;
+  for (size_t i = 0; i < v.size(); ++i)
+    if (v[i] > d->max_courant_num || (v[i] == d->max_courant_num && a[i] >= 0 && (arg < 0 || a[i] < arg))) { d->max_courant_num = v[i]; arg = a[i]; }
+  if (arg >= 0) {
+    /* arg = device cell * ELL width + slot: report the local edge id and the device cell's view-local id; the caller maps
+     * them to global ids with RDyEdges/RDyCells.global_ids as the reference does */
+    const int32_t cell = (int32_t)(arg / RDYB_ELL_WIDTH), slot = (int32_t)(arg % RDYB_ELL_WIDTH);
+    d->global_edge_id = op->L.ell_edge[(size_t)slot * op->L.stride + cell];
+    d->global_cell_id = op->L.dev_to_local[cell];
+  }
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_get_mass(RdybOperator op, double *mass) {
+  RDYB_CHECK(op && mass, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  mass_partial_kernel<<<1024, 256, 0, op->stream>>>(op->state[op->cur], op->area, op->N, op->partial);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  double host[1024];
+  CU(cudaMemcpyAsync(host, op->partial, sizeof(host), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  double s = 0.0;
+  for (int i = 0; i < 1024; ++i) s += host[i];
+  *mass = s;
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_device_pointer(RdybOperator op, int32_t which, void **ptr, int64_t *length) {
+  RDYB_CHECK(op && ptr, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(which >= 0 && which < 6, RDYB_ERR_ARG, "unknown array %d", which);
+  if (which < 3) { *ptr = op->state[op->cur] + (size_t)which * op->stride; if (length) *length = op->NL; }
+  else { *ptr = op->F + (size_t)(which - 3) * op->stride; if (length) *length = op->N; }
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_last_kernel_ms(RdybOperator op, double *ms_per_launch, int32_t *launches) {
+  RDYB_CHECK(op && ms_per_launch, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaSetDevice(op->device));
+  CU(cudaEventSynchronize(op->ev_t1));
+  float ms = 0.f;
+  CU(cudaEventElapsedTime(&ms, op->ev_t0, op->ev_t1));
+  *ms_per_launch = op->last_launches > 0 ? (double)ms / op->last_launches : 0.0;
+  if (launches) *launches = op->last_launches;
+  return RDYB_SUCCESS;
+}
+
+/* pinned host memory for the reference-facing host-Vec path (apply_host) */
+extern "C" int rdyb_host_alloc(size_t bytes, void **ptr) {
+  RDYB_CHECK(ptr, RDYB_ERR_ARG, "NULL argument");
+  CU(cudaMallocHost(ptr, bytes));
+  return RDYB_SUCCESS;
+}
+extern "C" int rdyb_host_free(void *ptr) {
+  if (ptr) CU(cudaFreeHost(ptr));
+  return RDYB_SUCCESS;
+}

@@ -1,0 +1,267 @@
+/* swe_kernels.cuh — sm_100a kernels of the SWE right-hand side + explicit stage update.
+ *
+ * K1 "gather": one thread per owned cell; the cell walks its ELL edge list (device_layout.h), gathers the neighbour's
+ * state, evaluates the Roe flux with the edge's own left/right orientation (so both cells of an edge compute the same
+ * bits and mass is conserved exactly), applies boundary conditions for boundary slots, then the bed-slope / friction /
+ * external sources of the cell, and either writes F (RHS mode: ApplyPetscOperator, src/operator.c:656-672) or the new
+ * state u + dt*F (Euler mode: + TSEULER).  No float atomics: the result is deterministic.
+ *
+ * Replaces, fused: ApplyInteriorFlux src/swe/swe_petsc.c:215-316, ApplyInteriorFluxHR :1000-1161, ApplyBoundaryFlux
+ * :506-630, ApplySourceSemiImplicit :704-804, ApplySourceImplicitXQ2018 :816-932, VecZeroEntries src/rdysetup.c:1130,
+ * the two VecCopy of src/operator.c:663,669 and the TS stage update.
+ */
+#ifndef RDYB_SWE_KERNELS_CUH
+#define RDYB_SWE_KERNELS_CUH
+
+#include <stdint.h>
+
+#include "device_layout.h"
+#include "rdyb200.h"
+#include "swe_math.cuh"
+
+#define RDYB_BLOCK 128
+
+struct SweArgs {
+  /* state in (device order, SoA, length n_local) */
+  const double *__restrict__ h, *__restrict__ hu, *__restrict__ hv;
+  /* out: F (RHS mode) or new state (Euler mode), SoA */
+  double *__restrict__ o0, *__restrict__ o1, *__restrict__ o2;
+  const double *__restrict__ inv_area, *__restrict__ dzdx, *__restrict__ dzdy, *__restrict__ zc, *__restrict__ mann;
+  const double *__restrict__ s0, *__restrict__ s1, *__restrict__ s2; /* external sources; s1,s2 may be NULL (all zero) */
+  const int32_t *__restrict__ nbr;
+  const double *__restrict__ esn, *__restrict__ ecn, *__restrict__ eslen;
+  /* boundary-edge table */
+  const int32_t *__restrict__ btype;
+  const double *__restrict__ bval; /* [3][nbe] */
+  double *__restrict__ bflux, *__restrict__ bacc; /* [3][nbe] or NULL */
+  int32_t nbe;
+  /* optional outputs (NULL = off): flux divergence and primitive variables, SoA [3][stride] */
+  double *__restrict__ fdiv, *__restrict__ prim;
+  /* Courant diagnostics: one slot per block (running max since reset), NULL = off */
+  double *__restrict__ cmax;
+  long long *__restrict__ carg;
+  int32_t stride, width, begin, end;
+  double dt, tiny_h, ha2, xq_thr;
+};
+
+__device__ __forceinline__ void courant_block_reduce(double cmax, long long carg, double *slot_val, long long *slot_arg) {
+  /* max over the block; ties go to the smaller arg so the result does not depend on scheduling */
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const double ov = __shfl_down_sync(0xffffffffu, cmax, off);
+    const long long oa = __shfl_down_sync(0xffffffffu, carg, off);
+    if (ov > cmax || (ov == cmax && oa >= 0 && (carg < 0 || oa < carg))) { cmax = ov; carg = oa; }
+  }
+  __shared__ double sval[RDYB_BLOCK / 32];
+  __shared__ long long sarg[RDYB_BLOCK / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { sval[warp] = cmax; sarg[warp] = carg; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < RDYB_BLOCK / 32; ++w)
+      if (sval[w] > cmax || (sval[w] == cmax && sarg[w] >= 0 && (carg < 0 || sarg[w] < carg))) { cmax = sval[w]; carg = sarg[w]; }
+    if (cmax > *slot_val) { *slot_val = cmax; *slot_arg = carg; } /* the block owns its slot: plain read-modify-write */
+  }
+}
+
+template <bool HR, int SRC, bool EULER, bool COURANT>
+__global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a) {
+  const int i = a.begin + blockIdx.x * RDYB_BLOCK + threadIdx.x;
+  double cmax = 0.0;
+  long long carg = -1;
+  if (i < a.end) {
+    const double g = RDYB_GRAVITY;
+    const double tiny = a.tiny_h;
+    const double h = a.h[i], hu = a.hu[i], hv = a.hv[i];
+    const double ia = a.inv_area[i];
+    double u, v;
+    swe_velocities<HR>(h, hu, hv, tiny, a.ha2, u, v);
+    const double zc = HR ? a.zc[i] : 0.0;
+    double F0 = 0.0, F1 = 0.0, F2 = 0.0;
+#pragma unroll
+    for (int k = 0; k < RDYB_ELL_WIDTH; ++k) {
+      if (k >= a.width) break;
+      const size_t q = (size_t)k * (size_t)a.stride + (size_t)i;
+      const int nbr = a.nbr[q];
+      if (nbr == RDYB_NO_EDGE) continue;
+      const double sn = a.esn[q], cn = a.ecn[q], slen = a.eslen[q];
+      const double scale = slen * ia; /* -L/A when this cell is the left cell, +L/A when it is the right cell */
+      if (nbr >= 0) {
+        const double hn = a.h[nbr];
+        if (hn < tiny && h < tiny) continue; /* src/swe/swe_petsc.c:285, :1096 */
+        const double hun = a.hu[nbr], hvn = a.hv[nbr];
+        double un, vn;
+        swe_velocities<HR>(hn, hun, hvn, tiny, a.ha2, un, vn);
+        const bool left = slen < 0.0;
+        double hl = left ? h : hn, ul = left ? u : un, vl = left ? v : vn;
+        double hr = left ? hn : h, ur = left ? un : u, vr = left ? vn : v;
+        bool do_flux = true;
+        double c1 = 0.0, c2 = 0.0;
+        if (HR) {
+          /* hydrostatic reconstruction, src/swe/swe_petsc.c:1060-1075 */
+          const double zn = a.zc[nbr];
+          const double zl = left ? zc : zn, zr = left ? zn : zc;
+          const double zmax = fmax(zl, zr);
+          const double hls = fmax(0.0, (hl + zl) - zmax), hrs = fmax(0.0, (hr + zr) - zmax);
+          /* pressure correction on this cell's side, outside the inner guard (:1137-1154) */
+          const double hme = left ? hls : hrs;
+          const double corr = 0.5 * g * (h * h - hme * hme);
+          c1 = corr * cn * scale;
+          c2 = corr * sn * scale;
+          hl = hls;
+          hr = hrs;
+          do_flux = (hls > tiny || hrs > tiny);
+        }
+        if (do_flux) {
+          const RoeFlux f = swe_roe_flux(hl, ul, vl, hr, ur, vr, sn, cn);
+          if (COURANT) {
+            const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * a.dt; /* amax*L/min(A_l,A_r)*dt */
+            if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
+          }
+          F0 += f.f0 * scale;
+          F1 += f.f1 * scale;
+          F2 += f.f2 * scale;
+        }
+        if (HR) { F1 += c1; F2 += c2; }
+      } else {
+        /* boundary edge: the cell is the left cell; ApplyBoundaryFlux uses the non-strict wet test for both operators */
+        const int j = -(nbr + 1);
+        double ul, vl;
+        swe_velocities<false>(h, hu, hv, tiny, a.ha2, ul, vl);
+        double hr = 0.0, ur = 0.0, vr = 0.0;
+        bool ok = true;
+        const int type = a.btype[j];
+        if (type == RDYB_CONDITION_DIRICHLET) {
+          hr = a.bval[j];
+          swe_velocities<false>(hr, a.bval[a.nbe + j], a.bval[2 * a.nbe + j], tiny, a.ha2, ur, vr);
+        } else if (type == RDYB_CONDITION_REFLECTING) {
+          swe_reflecting_bc(h, ul, vl, sn, cn, hr, ur, vr);
+        } else {
+          ok = swe_critical_outflow_bc(h, ul, vl, sn, cn, hr, ur, vr);
+        }
+        RoeFlux f = {0.0, 0.0, 0.0, 0.0};
+        if (ok && !(h < tiny && hr < tiny)) {
+          f = swe_roe_flux(h, ul, vl, hr, ur, vr, sn, cn);
+          if (COURANT) {
+            const double cnum = f.amax * fabs(slen) * ia * a.dt;
+            if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
+          }
+          F0 += f.f0 * scale;
+          F1 += f.f1 * scale;
+          F2 += f.f2 * scale;
+        }
+        if (a.bflux) { /* boundary_fluxes and boundary_fluxes_accum += dt*flux, src/swe/swe_petsc.c:623 */
+          a.bflux[j] = f.f0; a.bflux[a.nbe + j] = f.f1; a.bflux[2 * a.nbe + j] = f.f2;
+          a.bacc[j] += a.dt * f.f0; a.bacc[a.nbe + j] += a.dt * f.f1; a.bacc[2 * a.nbe + j] += a.dt * f.f2;
+        }
+      }
+    }
+    if (a.fdiv) { a.fdiv[i] = F0; a.fdiv[a.stride + i] = F1; a.fdiv[2 * a.stride + i] = F2; }
+    /* sources */
+    double bedx = 0.0, bedy = 0.0, tbx = 0.0, tby = 0.0;
+    if (!HR) { bedx = a.dzdx[i] * g * h; bedy = a.dzdy[i] * g * h; }
+    if (h >= tiny) swe_friction<SRC>(h, hu, hv, F1, F2, bedx, bedy, a.mann[i], a.dt, a.xq_thr, tbx, tby);
+    const double S1 = a.s1 ? a.s1[i] : 0.0, S2 = a.s2 ? a.s2[i] : 0.0;
+    F0 += a.s0[i];
+    F1 += -bedx - tbx + S1;
+    F2 += -bedy - tby + S2;
+    if (a.prim) {
+      const bool wet = h >= tiny;
+      const double r = h / (h * h + a.ha2);
+      a.prim[i] = h; a.prim[a.stride + i] = wet ? hu * r : 0.0; a.prim[2 * a.stride + i] = wet ? hv * r : 0.0;
+    }
+    if (EULER) {
+      a.o0[i] = h + a.dt * F0;
+      a.o1[i] = hu + a.dt * F1;
+      a.o2[i] = hv + a.dt * F2;
+    } else {
+      a.o0[i] = F0;
+      a.o1[i] = F1;
+      a.o2[i] = F2;
+    }
+  }
+  if (COURANT && a.cmax) courant_block_reduce(cmax, carg, &a.cmax[blockIdx.x], &a.carg[blockIdx.x]);
+}
+
+/* ---- layout conversion between the reference's AoS Vecs and the device SoA ---- */
+/* dst SoA[c*stride + d] = src AoS[3*map[d] + c] for d in [0,n) */
+__global__ void aos_to_soa_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n, int32_t stride) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d < n) {
+    const size_t s = 3 * (size_t)map[d];
+    dst[d] = src[s]; dst[stride + d] = src[s + 1]; dst[2 * stride + d] = src[s + 2];
+  }
+}
+/* dst AoS[3*map[d] + c] = src SoA[c*stride + d] */
+__global__ void soa_to_aos_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n, int32_t stride) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d < n) {
+    const size_t s = 3 * (size_t)map[d];
+    dst[s] = src[d]; dst[s + 1] = src[stride + d]; dst[s + 2] = src[2 * stride + d];
+  }
+}
+/* dst[d] = src[map[d]] / dst[map[d]] = src[d] */
+__global__ void gather_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d < n) dst[d] = src[map[d]];
+}
+__global__ void scatter_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n) {
+  const int d = blockIdx.x * blockDim.x + threadIdx.x;
+  if (d < n) dst[map[d]] = src[d];
+}
+
+/* halo pack: buf[c*nsend + k] = state[c*stride + cells[k]] (replaces the PetscSF pack of DMGlobalToLocal, src/rdysetup.c:1133) */
+__global__ void halo_pack_kernel(const double *__restrict__ state, const int32_t *__restrict__ cells, double *__restrict__ buf, int32_t nsend,
+                                 int32_t stride) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < nsend) {
+    const int c = cells[k];
+    buf[k] = state[c]; buf[nsend + k] = state[stride + c]; buf[2 * nsend + k] = state[2 * stride + c];
+  }
+}
+/* halo unpack: ghosts of all peers are the contiguous device cells [n_owned, n_owned+nrecv) */
+__global__ void halo_unpack_kernel(const double *__restrict__ buf, double *__restrict__ state, int32_t nrecv, int32_t n_owned, int32_t stride) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < nrecv) {
+    state[n_owned + k] = buf[k]; state[stride + n_owned + k] = buf[nrecv + k]; state[2 * stride + n_owned + k] = buf[2 * nrecv + k];
+  }
+}
+
+/* y[c*stride+i] = x[c*stride+i] + w*k[c*stride+i], i < n (TSRK4 stage vectors) */
+__global__ void stage_axpy_kernel(const double *__restrict__ x, const double *__restrict__ k, double w, double *__restrict__ y, int32_t n, int32_t stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) y[c * (size_t)stride + i] = x[c * (size_t)stride + i] + w * k[c * (size_t)stride + i];
+  }
+}
+/* u += w0*k0, then += w1*k1, ... in that order (VecMAXPY-like, sequential per entry) */
+__global__ void rk4_combine_kernel(double *__restrict__ u, const double *__restrict__ k0, const double *__restrict__ k1, const double *__restrict__ k2,
+                                   const double *__restrict__ k3, double w0, double w1, double w2, double w3, int32_t n, int32_t stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const size_t q = c * (size_t)stride + i;
+      double x = u[q];
+      x += w0 * k0[q]; x += w1 * k1[q]; x += w2 * k2[q]; x += w3 * k3[q];
+      u[q] = x;
+    }
+  }
+}
+
+/* deterministic two-stage sum of area*h over owned cells: fixed blocks, fixed tree */
+__global__ void mass_partial_kernel(const double *__restrict__ h, const double *__restrict__ area, int32_t n, double *__restrict__ partial) {
+  __shared__ double s[256];
+  double acc = 0.0;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) acc += area[i] * h[i];
+  s[threadIdx.x] = acc;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if ((int)threadIdx.x < off) s[threadIdx.x] += s[threadIdx.x + off];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) partial[blockIdx.x] = s[0];
+}
+
+#endif
