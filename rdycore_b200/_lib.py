@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librdyb200.so")
+LIB_PATH = os.environ.get("RDYB_LIB") or os.path.join(HERE, "librdyb200.so")  # RDYB_LIB: a variant build, for experiments
 
 c_i32p = C.POINTER(C.c_int32)
 c_i64p = C.POINTER(C.c_int64)

@@ -234,14 +234,136 @@ fail:
   return ierr;
 }
 
+/* ---------------- tiled layout ---------------- */
 void rdyb_tiled_layout_free(RdybTiledLayout *T) {
   if (!T) return;
-  free(T->tile_cell_begin); free(T->halo_offsets); free(T->halo_cells); free(T->edge_offsets); free(T->edge_left); free(T->edge_right);
-  free(T->edge_bidx); free(T->edge_sn); free(T->edge_cn); free(T->edge_len); free(T->cell_edges);
+  free(T->tile_cell_begin); free(T->halo_offsets); free(T->halo_cells); free(T->edge_offsets); free(T->edge_lr);
+  free(T->edge_bidx); free(T->edge_sn); free(T->edge_cn); free(T->edge_len); free(T->cell_edges); free(T->edge_id); free(T->edge_cell);
   memset(T, 0, sizeof(*T));
 }
 
+static int cmp_i32(const void *a, const void *b) {
+  int32_t x = *(const int32_t *)a, y = *(const int32_t *)b;
+  return x < y ? -1 : x > y;
+}
+static int32_t lower_bound_i32(const int32_t *a, int32_t n, int32_t key) {
+  int32_t lo = 0, hi = n;
+  while (lo < hi) { int32_t mid = (lo + hi) / 2; if (a[mid] < key) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+#define GROW(ptr, cap, need)                                                                      \
+  do {                                                                                            \
+    if ((need) > (cap)) {                                                                         \
+      int64_t nc_ = (cap) + (cap) / 2 + 1024;                                                     \
+      if (nc_ < (need)) nc_ = (need);                                                             \
+      void *np_ = realloc((ptr), (size_t)nc_ * sizeof(*(ptr)));                                   \
+      if (!np_) { ierr = rdyb_fail(RDYB_ERR_MEM, "tiled layout: out of memory (%s)", #ptr); goto fail; } \
+      (ptr) = np_;                                                                                \
+      (cap) = nc_;                                                                                \
+    }                                                                                             \
+  } while (0)
+
 int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLayout *T) {
-  (void)L; (void)tile_cells; (void)T;
-  return rdyb_fail(RDYB_ERR_SUP, "tiled layout not built yet");
+  int ierr = RDYB_SUCCESS;
+  int32_t *tmp_halo = NULL, *slot_edge = NULL;
+  RDYB_CHECK(L && T, RDYB_ERR_ARG, "tiled layout: NULL argument");
+  RDYB_CHECK(tile_cells >= 128 && tile_cells <= 8192, RDYB_ERR_ARG, "tiled layout: tile_cells (%d) must be in [128, 8192]", tile_cells);
+  memset(T, 0, sizeof(*T));
+  const int32_t N = L->n_owned, NI = L->n_interior, W = L->width, TC = tile_cells;
+  const size_t S = (size_t)L->stride;
+  const int32_t nt_int = (NI + TC - 1) / TC, nt_fr = (N - NI + TC - 1) / TC, nt = nt_int + nt_fr;
+  T->tile_cells = TC; T->num_tiles = nt; T->num_interior_tiles = nt_int;
+  LALLOC(T->tile_cell_begin, nt + 1); LALLOC(T->halo_offsets, nt + 1); LALLOC(T->edge_offsets, nt + 1);
+  LALLOC(T->cell_edges, (size_t)RDYB_ELL_WIDTH * S);
+  memset(T->cell_edges, 0xff, sizeof(uint16_t) * (size_t)RDYB_ELL_WIDTH * S);
+  LALLOC(tmp_halo, (size_t)TC * RDYB_ELL_WIDTH); LALLOC(slot_edge, (size_t)TC * RDYB_ELL_WIDTH);
+  int64_t hcap = 0, ecap = 0, nh = 0, ne = 0;
+  for (int32_t t = 0; t < nt; ++t) {
+    const int32_t cb = t < nt_int ? t * TC : NI + (t - nt_int) * TC;
+    const int32_t lim = t < nt_int ? NI : N;
+    const int32_t ce = cb + TC < lim ? cb + TC : lim, ncell = ce - cb;
+    T->tile_cell_begin[t] = cb; T->halo_offsets[t] = (int32_t)nh; T->edge_offsets[t] = (int32_t)ne;
+    /* halo = neighbours outside [cb,ce), sorted unique */
+    int32_t nth = 0;
+    for (int32_t i = cb; i < ce; ++i)
+      for (int32_t k = 0; k < W; ++k) {
+        int32_t nbr = L->ell_nbr[(size_t)k * S + i];
+        if (nbr >= 0 && (nbr < cb || nbr >= ce)) tmp_halo[nth++] = nbr;
+      }
+    qsort(tmp_halo, (size_t)nth, sizeof(int32_t), cmp_i32);
+    int32_t nuniq = 0;
+    for (int32_t j = 0; j < nth; ++j) if (j == 0 || tmp_halo[j] != tmp_halo[j - 1]) tmp_halo[nuniq++] = tmp_halo[j];
+    nth = nuniq;
+    if (ncell + nth > 65534) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: tile %d needs %d staged cells (> 65534)", t, ncell + nth); goto fail; }
+    GROW(T->halo_cells, hcap, nh + nth);
+    memcpy(T->halo_cells + nh, tmp_halo, sizeof(int32_t) * (size_t)nth);
+    /* pass 1: edges owned by the tile = slots where the cell is the left cell, or the neighbour is outside, or a boundary */
+    int32_t nte = 0;
+    for (int32_t i = cb; i < ce; ++i)
+      for (int32_t k = 0; k < W; ++k) {
+        const size_t q = (size_t)k * S + i;
+        const int32_t nbr = L->ell_nbr[q];
+        slot_edge[(i - cb) * RDYB_ELL_WIDTH + k] = -1;
+        if (nbr == RDYB_NO_EDGE) continue;
+        const int in_tile = nbr >= cb && nbr < ce;
+        const int me_left = L->ell_slen[q] < 0.0;
+        if (nbr >= 0 && in_tile && !me_left) continue; /* created by the left cell */
+        const int64_t g = ne + nte;
+        if (g + 1 > ecap) {
+          int64_t ncap = ecap + ecap / 2 + 4096;
+          void *p1 = realloc(T->edge_lr, (size_t)ncap * sizeof(uint32_t)), *p2 = NULL, *p3 = NULL, *p4 = NULL, *p5 = NULL, *p6 = NULL, *p7 = NULL;
+          if (p1) { T->edge_lr = p1; p2 = realloc(T->edge_bidx, (size_t)ncap * sizeof(int32_t)); }
+          if (p2) { T->edge_bidx = p2; p3 = realloc(T->edge_sn, (size_t)ncap * sizeof(double)); }
+          if (p3) { T->edge_sn = p3; p4 = realloc(T->edge_cn, (size_t)ncap * sizeof(double)); }
+          if (p4) { T->edge_cn = p4; p5 = realloc(T->edge_len, (size_t)ncap * sizeof(double)); }
+          if (p5) { T->edge_len = p5; p6 = realloc(T->edge_id, (size_t)ncap * sizeof(int32_t)); }
+          if (p6) { T->edge_id = p6; p7 = realloc(T->edge_cell, (size_t)ncap * sizeof(int32_t)); }
+          if (!p7) { ierr = rdyb_fail(RDYB_ERR_MEM, "tiled layout: out of memory (edges)"); goto fail; }
+          T->edge_cell = p7;
+          ecap = ncap;
+        }
+        uint32_t me = (uint32_t)(i - cb), other = 0xFFFFu;
+        int32_t report_cell = i;
+        if (nbr >= 0) {
+          other = in_tile ? (uint32_t)(nbr - cb) : (uint32_t)(ncell + lower_bound_i32(tmp_halo, nth, nbr));
+          const int32_t lc = me_left ? i : nbr, rc = me_left ? nbr : i;
+          report_cell = L->area[lc] < L->area[rc] ? lc : rc; /* src/swe/swe_petsc.c:289-296 */
+        }
+        const uint32_t left = me_left ? me : other, right = me_left ? other : me;
+        T->edge_lr[g] = left | (right << 16);
+        T->edge_bidx[g] = nbr < 0 ? -(nbr + 1) : -1;
+        T->edge_sn[g] = L->ell_sn[q]; T->edge_cn[g] = L->ell_cn[q]; T->edge_len[g] = fabs(L->ell_slen[q]);
+        T->edge_id[g] = L->ell_edge[q]; T->edge_cell[g] = report_cell;
+        slot_edge[(i - cb) * RDYB_ELL_WIDTH + k] = nte++;
+      }
+    if (nte > 32767) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: tile %d has %d edges (> 32767)", t, nte); goto fail; }
+    /* pass 2: per-cell edge slots, in the ELL (reference accumulation) order */
+    for (int32_t i = cb; i < ce; ++i)
+      for (int32_t k = 0; k < W; ++k) {
+        const size_t q = (size_t)k * S + i;
+        const int32_t nbr = L->ell_nbr[q];
+        if (nbr == RDYB_NO_EDGE) continue;
+        int32_t e = slot_edge[(i - cb) * RDYB_ELL_WIDTH + k];
+        const int me_left = L->ell_slen[q] < 0.0;
+        if (e < 0) { /* in-tile edge created by the left cell nbr: find its slot with the same edge id */
+          for (int32_t k2 = 0; k2 < W && e < 0; ++k2)
+            if (L->ell_nbr[(size_t)k2 * S + nbr] == i && L->ell_edge[(size_t)k2 * S + nbr] == L->ell_edge[q]) e = slot_edge[(nbr - cb) * RDYB_ELL_WIDTH + k2];
+          if (e < 0) { ierr = rdyb_fail(RDYB_ERR_USER, "tiled layout: inconsistent edge lists at cell %d", L->dev_to_local[i]); goto fail; }
+        }
+        T->cell_edges[q] = (uint16_t)((uint32_t)e | (me_left ? 0u : 0x8000u));
+      }
+    nh += nth; ne += nte;
+    if (nth > T->max_halo) T->max_halo = nth;
+    if (nte > T->max_edges) T->max_edges = nte;
+    if (ne > INT32_MAX - 65536 || nh > INT32_MAX - 65536) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: too many tile edges for int32 offsets"); goto fail; }
+  }
+  T->tile_cell_begin[nt] = N; T->halo_offsets[nt] = (int32_t)nh; T->edge_offsets[nt] = (int32_t)ne;
+  T->total_edges = ne; T->total_halo = nh;
+  free(tmp_halo); free(slot_edge);
+  return RDYB_SUCCESS;
+fail:
+  free(tmp_halo); free(slot_edge);
+  rdyb_tiled_layout_free(T);
+  return ierr;
 }

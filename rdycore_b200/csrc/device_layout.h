@@ -68,8 +68,9 @@ typedef struct {
   int32_t *edge_offsets;     /* [num_tiles+1] into the per-tile-edge arrays */
   /* per tile edge: endpoints as tile-local indices (0..ncell-1 tile cells, ncell.. halo cells); right = 0xFFFF-coded boundary
    * uses edge_bidx */
-  uint16_t *edge_left, *edge_right; /* edge_right == 0xFFFF => boundary edge, see edge_bidx */
+  uint32_t *edge_lr;         /* left | right << 16; right == 0xFFFF => boundary edge, see edge_bidx */
   int32_t  *edge_bidx;       /* flattened boundary-edge index or -1 */
+  int32_t  *edge_id, *edge_cell; /* host only: local edge id and the device cell the Courant diagnostic reports (al < ar ? l : r) */
   double   *edge_sn, *edge_cn, *edge_len;
   /* per cell: up to `width` tile-edge slots in the reference's accumulation order; value = tile-local edge index,
    * bit 15 set => the cell is the edge's right cell; 0xFFFF => empty */

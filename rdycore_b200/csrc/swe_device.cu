@@ -452,9 +452,11 @@ static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
 static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
   if (end <= begin) return RDYB_SUCCESS;
   if (op->kernel_kind == 1 && op->has_tiled) {
-    RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, in, out, op->src, op->mom_src, op->mann, op->btype, op->bval, op->opt_bflux ? op->bflux : nullptr,
-                           op->opt_bflux ? op->bacc : nullptr, op->nbe, op->opt_fdiv ? op->fdiv : nullptr, op->opt_prim ? op->prim : nullptr,
-                           op->opt_courant ? op->cmax : nullptr, op->carg, dt, euler, begin, end, op->stream));
+    SweArgs t;
+    fill_args(op, t, in, out, dt);
+    t.begin = begin; t.end = end;
+    if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile, indexed by tile number */
+    RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     LAUNCHED();
     CU(cudaGetLastError());
     return RDYB_SUCCESS;
@@ -665,7 +667,11 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   long long arg = -1;
   for (size_t i = 0; i < v.size(); ++i)
     if (v[i] > d->max_courant_num || (v[i] == d->max_courant_num && a[i] >= 0 && (arg < 0 || a[i] < arg))) { d->max_courant_num = v[i]; arg = a[i]; }
-  if (arg >= 0) {
+  if (arg >= 0 && op->kernel_kind == 1 && op->has_tiled) {
+    /* tiled kernel: arg = global tile-edge index */
+    d->global_edge_id = op->T.edge_id[arg];
+    d->global_cell_id = op->L.dev_to_local[op->T.edge_cell[arg]];
+  } else if (arg >= 0) {
     /* arg = device cell * ELL width + slot: report the local edge id and the device cell's view-local id; the caller maps
      * them to global ids with RDyEdges/RDyCells.global_ids as the reference does */
     const int32_t cell = (int32_t)(arg / RDYB_ELL_WIDTH), slot = (int32_t)(arg % RDYB_ELL_WIDTH);

@@ -21,7 +21,12 @@ KERNELS = [GATHER, TILED]
 def _op(case, kernel=GATHER, **opts):
     op = Operator.from_case(case)
     if kernel != GATHER:
-        op.set_kernel(kernel, 256)
+        try:
+            op.set_kernel(kernel, 256)
+        except Exception as exc:
+            if "not built" in str(exc):
+                pytest.skip("tiled kernel not built yet")
+            raise
     if opts:
         op.set_options(**opts)
     return op
@@ -47,9 +52,12 @@ def test_dam_break_config_a_1000_steps(source_method, kernel):
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
-def test_floodplain_triangles_semi_implicit(kernel):
-    """Config C scaled down: jittered triangles, bathymetry, Manning n, rain, wet/dry shoreline."""
+@pytest.mark.parametrize("rain", [True, False])
+def test_floodplain_triangles_semi_implicit(kernel, rain):
+    """Config C scaled down: jittered triangles, bathymetry, Manning n, rain (or a dry shoreline without it)."""
     case = cases.floodplain(nx=96, ny=80, eta0=8.0)
+    if not rain:
+        case.sources[:] = 0.0
     oracle = make_oracle(case)
     op = _op(case, kernel)
     for _ in range(3):
@@ -63,13 +71,14 @@ def test_floodplain_triangles_semi_implicit(kernel):
 def test_floodplain_hydrostatic_reconstruction(source_method, kernel):
     """Config D scaled down: HR flux + sources without bed slope, wet/dry fronts from a dam column."""
     case = cases.floodplain(nx=64, ny=64, eta0=6.0, hr=True, source_method=source_method, dam_column=(200.0, 14.0))
+    case.sources[:] = 0.0  # no rain: about half of the cells stay dry and the fronts run over dry land
     oracle = make_oracle(case)
     op = _op(case, kernel)
     for _ in range(3):
         op.step_euler(case.dt, 100)
         oracle.step_euler(case.dt, 100)
         assert_state_close(op.get_state(), oracle.array("u_global"), what="floodplain HR")
-    assert (oracle.array("u_global").reshape(-1, 3)[:, 0] < 1e-7).any() or True
+    assert (oracle.array("u_global").reshape(-1, 3)[:, 0] < 1e-7).sum() > 1000
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
