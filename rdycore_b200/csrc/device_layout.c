@@ -128,6 +128,9 @@ int rdyb_layout_build(const RdybMeshView *mv, int32_t nb, const RdybBoundaryView
       L->owned_to_dev[mv->cell_local_to_owned[c]] = d; L->dev_to_owned[d] = mv->cell_local_to_owned[c];
       if (!frontier[c]) ++L->n_interior;
     }
+    /* the last (< 8) interior cells are treated as frontier so that both ranges start on a multiple of 8 cells
+     * (16-byte alignment of every per-cell slice a tile fetches with a bulk async copy) */
+    if (L->n_interior < N) L->n_interior &= ~7;
   }
   /* ghosts: per peer in recv order, then the remaining non-owned cells in ascending local id */
   {
@@ -238,7 +241,7 @@ fail:
 void rdyb_tiled_layout_free(RdybTiledLayout *T) {
   if (!T) return;
   free(T->tile_cell_begin); free(T->halo_offsets); free(T->halo_cells); free(T->edge_offsets); free(T->edge_lr);
-  free(T->edge_bidx); free(T->edge_sn); free(T->edge_cn); free(T->edge_len); free(T->cell_edges); free(T->edge_id); free(T->edge_cell);
+  free(T->edge_bidx); free(T->edge_sn); free(T->edge_cn); free(T->edge_len); free(T->cell_edges); free(T->edge_id); free(T->edge_cell); free(T->tile_desc);
   memset(T, 0, sizeof(*T));
 }
 
@@ -264,17 +267,34 @@ static int32_t lower_bound_i32(const int32_t *a, int32_t n, int32_t key) {
     }                                                                                             \
   } while (0)
 
+static int edges_reserve(RdybTiledLayout *T, int64_t *cap, int64_t need) {
+  if (need <= *cap) return RDYB_SUCCESS;
+  int64_t ncap = *cap + *cap / 2 + 4096;
+  if (ncap < need) ncap = need;
+  void *p;
+#define RES(field, type)                                                                      \
+  p = realloc(T->field, (size_t)ncap * sizeof(type));                                         \
+  if (!p) return rdyb_fail(RDYB_ERR_MEM, "tiled layout: out of memory (edges)");              \
+  T->field = p;
+  RES(edge_lr, uint32_t) RES(edge_bidx, int32_t) RES(edge_sn, double) RES(edge_cn, double) RES(edge_len, double) RES(edge_id, int32_t)
+  RES(edge_cell, int32_t)
+#undef RES
+  *cap = ncap;
+  return RDYB_SUCCESS;
+}
+
 int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLayout *T) {
   int ierr = RDYB_SUCCESS;
   int32_t *tmp_halo = NULL, *slot_edge = NULL;
   RDYB_CHECK(L && T, RDYB_ERR_ARG, "tiled layout: NULL argument");
-  RDYB_CHECK(tile_cells >= 128 && tile_cells <= 8192, RDYB_ERR_ARG, "tiled layout: tile_cells (%d) must be in [128, 8192]", tile_cells);
+  RDYB_CHECK(tile_cells >= 128 && tile_cells <= 8192 && tile_cells % 8 == 0, RDYB_ERR_ARG, "tiled layout: tile_cells (%d) must be a multiple of 8 in [128, 8192]", tile_cells);
   memset(T, 0, sizeof(*T));
   const int32_t N = L->n_owned, NI = L->n_interior, W = L->width, TC = tile_cells;
   const size_t S = (size_t)L->stride;
   const int32_t nt_int = (NI + TC - 1) / TC, nt_fr = (N - NI + TC - 1) / TC, nt = nt_int + nt_fr;
   T->tile_cells = TC; T->num_tiles = nt; T->num_interior_tiles = nt_int;
   LALLOC(T->tile_cell_begin, nt + 1); LALLOC(T->halo_offsets, nt + 1); LALLOC(T->edge_offsets, nt + 1);
+  LALLOC(T->tile_desc, 8 * (size_t)nt);
   LALLOC(T->cell_edges, (size_t)RDYB_ELL_WIDTH * S);
   memset(T->cell_edges, 0xff, sizeof(uint16_t) * (size_t)RDYB_ELL_WIDTH * S);
   LALLOC(tmp_halo, (size_t)TC * RDYB_ELL_WIDTH); LALLOC(slot_edge, (size_t)TC * RDYB_ELL_WIDTH);
@@ -283,6 +303,17 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
     const int32_t cb = t < nt_int ? t * TC : NI + (t - nt_int) * TC;
     const int32_t lim = t < nt_int ? NI : N;
     const int32_t ce = cb + TC < lim ? cb + TC : lim, ncell = ce - cb;
+    /* tile starts are padded to 4 entries (16 bytes for the int32/uint32 arrays, 32 for the doubles) so that a tile's slice
+     * of every per-tile array can be fetched with one bulk async copy */
+    while (nh & 3) { GROW(T->halo_cells, hcap, nh + 1); T->halo_cells[nh++] = 0; }
+    if (ne & 3) {
+      int64_t pad = 4 - (ne & 3);
+      if (ne + pad > ecap) { ierr = edges_reserve(T, &ecap, ne + pad); if (ierr) goto fail; }
+      for (int64_t g = ne; g < ne + pad; ++g) {
+        T->edge_lr[g] = 0; T->edge_bidx[g] = -1; T->edge_sn[g] = 0.0; T->edge_cn[g] = 1.0; T->edge_len[g] = 0.0; T->edge_id[g] = -1; T->edge_cell[g] = -1;
+      }
+      ne += pad;
+    }
     T->tile_cell_begin[t] = cb; T->halo_offsets[t] = (int32_t)nh; T->edge_offsets[t] = (int32_t)ne;
     /* halo = neighbours outside [cb,ce), sorted unique */
     int32_t nth = 0;
@@ -295,7 +326,7 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
     int32_t nuniq = 0;
     for (int32_t j = 0; j < nth; ++j) if (j == 0 || tmp_halo[j] != tmp_halo[j - 1]) tmp_halo[nuniq++] = tmp_halo[j];
     nth = nuniq;
-    if (ncell + nth > 65534) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: tile %d needs %d staged cells (> 65534)", t, ncell + nth); goto fail; }
+    if (TC + nth > 65534) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: tile %d needs %d staged cells (> 65534)", t, ncell + nth); goto fail; }
     GROW(T->halo_cells, hcap, nh + nth);
     memcpy(T->halo_cells + nh, tmp_halo, sizeof(int32_t) * (size_t)nth);
     /* pass 1: edges owned by the tile = slots where the cell is the left cell, or the neighbour is outside, or a boundary */
@@ -310,23 +341,11 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
         const int me_left = L->ell_slen[q] < 0.0;
         if (nbr >= 0 && in_tile && !me_left) continue; /* created by the left cell */
         const int64_t g = ne + nte;
-        if (g + 1 > ecap) {
-          int64_t ncap = ecap + ecap / 2 + 4096;
-          void *p1 = realloc(T->edge_lr, (size_t)ncap * sizeof(uint32_t)), *p2 = NULL, *p3 = NULL, *p4 = NULL, *p5 = NULL, *p6 = NULL, *p7 = NULL;
-          if (p1) { T->edge_lr = p1; p2 = realloc(T->edge_bidx, (size_t)ncap * sizeof(int32_t)); }
-          if (p2) { T->edge_bidx = p2; p3 = realloc(T->edge_sn, (size_t)ncap * sizeof(double)); }
-          if (p3) { T->edge_sn = p3; p4 = realloc(T->edge_cn, (size_t)ncap * sizeof(double)); }
-          if (p4) { T->edge_cn = p4; p5 = realloc(T->edge_len, (size_t)ncap * sizeof(double)); }
-          if (p5) { T->edge_len = p5; p6 = realloc(T->edge_id, (size_t)ncap * sizeof(int32_t)); }
-          if (p6) { T->edge_id = p6; p7 = realloc(T->edge_cell, (size_t)ncap * sizeof(int32_t)); }
-          if (!p7) { ierr = rdyb_fail(RDYB_ERR_MEM, "tiled layout: out of memory (edges)"); goto fail; }
-          T->edge_cell = p7;
-          ecap = ncap;
-        }
+        if (g + 1 > ecap) { ierr = edges_reserve(T, &ecap, g + 1); if (ierr) goto fail; }
         uint32_t me = (uint32_t)(i - cb), other = 0xFFFFu;
         int32_t report_cell = i;
         if (nbr >= 0) {
-          other = in_tile ? (uint32_t)(nbr - cb) : (uint32_t)(ncell + lower_bound_i32(tmp_halo, nth, nbr));
+          other = in_tile ? (uint32_t)(nbr - cb) : (uint32_t)(TC + lower_bound_i32(tmp_halo, nth, nbr)); /* halo cells sit at TC + t */
           const int32_t lc = me_left ? i : nbr, rc = me_left ? nbr : i;
           report_cell = L->area[lc] < L->area[rc] ? lc : rc; /* src/swe/swe_petsc.c:289-296 */
         }
@@ -353,13 +372,19 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
         }
         T->cell_edges[q] = (uint16_t)((uint32_t)e | (me_left ? 0u : 0x8000u));
       }
+    { int32_t *d = &T->tile_desc[8 * (size_t)t]; d[0] = cb; d[1] = ncell; d[2] = (int32_t)ne; d[3] = nte; d[4] = (int32_t)nh; d[5] = nth; d[6] = 0; d[7] = 0; }
     nh += nth; ne += nte;
     if (nth > T->max_halo) T->max_halo = nth;
     if (nte > T->max_edges) T->max_edges = nte;
     if (ne > INT32_MAX - 65536 || nh > INT32_MAX - 65536) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: too many tile edges for int32 offsets"); goto fail; }
   }
   T->tile_cell_begin[nt] = N; T->halo_offsets[nt] = (int32_t)nh; T->edge_offsets[nt] = (int32_t)ne;
-  T->total_edges = ne; T->total_halo = nh;
+  /* slack so that bulk copies rounded up to 16 bytes stay inside the arrays */
+  GROW(T->halo_cells, hcap, nh + 16);
+  for (int j = 0; j < 16; ++j) T->halo_cells[nh + j] = 0;
+  if ((ierr = edges_reserve(T, &ecap, ne + 16))) goto fail;
+  for (int64_t g = ne; g < ne + 16; ++g) { T->edge_lr[g] = 0; T->edge_bidx[g] = -1; T->edge_sn[g] = 0.0; T->edge_cn[g] = 1.0; T->edge_len[g] = 0.0; T->edge_id[g] = -1; T->edge_cell[g] = -1; }
+  T->total_edges = ne + 16; T->total_halo = nh + 16;
   free(tmp_halo); free(slot_edge);
   return RDYB_SUCCESS;
 fail:

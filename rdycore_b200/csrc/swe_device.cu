@@ -19,6 +19,7 @@
 #include "rdyb_error.h"
 #include "swe_kernels.cuh"
 #include "swe_tiled.cuh"
+#include "swe_tiled_async.cuh"
 
 static std::atomic<int64_t> g_launches{0};
 
@@ -102,7 +103,7 @@ struct RdybOperator_ {
   /* tiled-kernel device arrays */
   TiledDev td;
   bool has_tiled = false;
-  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2) */
+  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3) */
   /* options */
   bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
   bool mom_src = false; /* any momentum external source set */
@@ -256,9 +257,9 @@ extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_
 /* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
-  RDYB_CHECK(kind == 0 || kind == 1, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
+  RDYB_CHECK(kind >= 0 && kind <= 2, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
   CU(cudaSetDevice(op->device));
-  if (kind == 1) {
+  if (kind >= 1) {
     if (op->has_tiled && op->T.tile_cells != tile_cells) {
       tiled_dev_free(&op->td);
       rdyb_tiled_layout_free(&op->T);
@@ -451,12 +452,13 @@ static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
 /* one RHS / Euler pass over owned device cells [begin,end) */
 static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
   if (end <= begin) return RDYB_SUCCESS;
-  if (op->kernel_kind == 1 && op->has_tiled) {
+  if (op->kernel_kind >= 1 && op->has_tiled) {
     SweArgs t;
     fill_args(op, t, in, out, dt);
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile, indexed by tile number */
-    RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    if (op->kernel_kind == 2) RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    else RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     LAUNCHED();
     CU(cudaGetLastError());
     return RDYB_SUCCESS;
@@ -546,13 +548,7 @@ static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool eu
     RDYB_CALL(halo_end(op));
     RDYB_CALL(launch_cells(op, in, out, dt, euler, op->NI, op->N, op->ncblocks_interior));
   } else {
-    if (op->NI > 0 && op->NI < op->N && op->kernel_kind == 0) {
-      /* serial with caller-filled ghosts: two ranges keep the Courant slots consistent with the exchange path */
-      RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->NI, 0));
-      RDYB_CALL(launch_cells(op, in, out, dt, euler, op->NI, op->N, op->ncblocks_interior));
-    } else {
-      RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->N, 0));
-    }
+    RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->N, 0)); /* ghosts (if any) were filled by the caller */
   }
   return RDYB_SUCCESS;
 }
@@ -667,7 +663,7 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   long long arg = -1;
   for (size_t i = 0; i < v.size(); ++i)
     if (v[i] > d->max_courant_num || (v[i] == d->max_courant_num && a[i] >= 0 && (arg < 0 || a[i] < arg))) { d->max_courant_num = v[i]; arg = a[i]; }
-  if (arg >= 0 && op->kernel_kind == 1 && op->has_tiled) {
+  if (arg >= 0 && op->kernel_kind >= 1 && op->has_tiled) {
     /* tiled kernel: arg = global tile-edge index */
     d->global_edge_id = op->T.edge_id[arg];
     d->global_cell_id = op->L.dev_to_local[op->T.edge_cell[arg]];

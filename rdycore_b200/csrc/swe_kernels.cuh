@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
     double u, v;
     swe_velocities<HR>(h, hu, hv, tiny, a.ha2, u, v);
     const double zc = HR ? a.zc[i] : 0.0;
+    const double sq = swe_sqrt(h); /* HR re-evaluates it on the reconstructed depth */
     double F0 = 0.0, F1 = 0.0, F2 = 0.0;
 #pragma unroll
     for (int k = 0; k < RDYB_ELL_WIDTH; ++k) {
@@ -113,7 +114,10 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
           do_flux = (hls > tiny || hrs > tiny);
         }
         if (do_flux) {
-          const RoeFlux f = swe_roe_flux(hl, ul, vl, hr, ur, vr, sn, cn);
+          double sql, sqr;
+          if (HR) { sql = swe_sqrt(hl); sqr = swe_sqrt(hr); }
+          else { const double sqn = swe_sqrt(hn); sql = left ? sq : sqn; sqr = left ? sqn : sq; }
+          const RoeFlux f = swe_roe_flux(hl, ul, vl, sql, hr, ur, vr, sqr, sn, cn);
           if (COURANT) {
             const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * a.dt; /* amax*L/min(A_l,A_r)*dt */
             if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
@@ -141,7 +145,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
         }
         RoeFlux f = {0.0, 0.0, 0.0, 0.0};
         if (ok && !(h < tiny && hr < tiny)) {
-          f = swe_roe_flux(h, ul, vl, hr, ur, vr, sn, cn);
+          f = swe_roe_flux(h, ul, vl, swe_sqrt(h), hr, ur, vr, swe_sqrt(hr), sn, cn);
           if (COURANT) {
             const double cnum = f.amax * fabs(slen) * ia * a.dt;
             if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
@@ -167,7 +171,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
     F2 += -bedy - tby + S2;
     if (a.prim) {
       const bool wet = h >= tiny;
-      const double r = h / (h * h + a.ha2);
+      const double r = h * swe_rcp(h * h + a.ha2);
       a.prim[i] = h; a.prim[a.stride + i] = wet ? hu * r : 0.0; a.prim[2 * a.stride + i] = wet ? hv * r : 0.0;
     }
     if (EULER) {

@@ -10,6 +10,40 @@
 
 #define RDYB_GRAVITY 9.806 /* src/swe/swe_types_petsc.h:7 */
 
+#define RDYB_SQRT_GRAVITY 3.1314533367112465 /* sqrt of the double 9.806 */
+
+/* ---- branch-free fp64 reciprocal / rsqrt / sqrt ----
+ * MUFU seed (rcp.approx / rsqrt.approx, ~2^-20) + two Newton steps -> <= ~1 ulp, without the denormal / inf / NaN slow
+ * path that the IEEE-rounded `1.0/x` and `sqrt(x)` sequences carry (a CALL plus ~10 integer instructions each).  Valid
+ * for normal, positive, finite arguments, which is all this path produces (depths in [tiny_h, ~1e4], areas, speeds). */
+__device__ __forceinline__ double swe_rcp(double a) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  double e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  e = fma(-a, y, 1.0);
+  y = fma(y, e, y);
+  return y;
+}
+__device__ __forceinline__ double swe_rsqrt(double a) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  const double ha = 0.5 * a;
+  double e = fma(-ha, y * y, 0.5);
+  y = fma(y, e, y);
+  e = fma(-ha, y * y, 0.5);
+  y = fma(y, e, y);
+  return y;
+}
+/* sqrt(a) for a >= 0 (exactly 0 for a == 0); one Heron correction after a*rsqrt(a) */
+__device__ __forceinline__ double swe_sqrt(double a) {
+  const double y = swe_rsqrt(a);
+  double s = a * y;
+  const double r = fma(-s, s, a);
+  s = fma(r, 0.5 * y, s);
+  return a > 0.0 ? s : 0.0;
+}
+
 struct RoeFlux {
   double f0, f1, f2, amax;
 };
@@ -20,7 +54,7 @@ template <bool STRICT>
 __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, double tiny_h, double ha2, double &u, double &v) {
   const bool wet = STRICT ? (h > tiny_h) : !(h < tiny_h);
   if (wet) {
-    const double r = h / (h * h + ha2);
+    const double r = h * swe_rcp(h * h + ha2);
     u = hu * r;
     v = hv * r;
   } else {
@@ -30,17 +64,21 @@ __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, d
 }
 
 /* ComputeSWERoeEigenspectrum + the flux loop of ComputeSWERoeFlux, src/swe/swe_roe_flux_petsc.h:15-81, 108-128.
- * Inputs are (h,u,v) of the left and right state and the edge normal (cn,sn).  At least one of hl,hr must be > 0. */
-__device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl, double hr, double ur, double vr, double sn, double cn) {
+ * Inputs are (h,u,v,sqrt h) of the left and right state and the edge normal (cn,sn).  At least one of hl,hr must be > 0.
+ * Re-association vs the reference: sqrt(g h) = sqrt(g) sqrt(h); chat and 1/chat from one rsqrt; one shared 1/(duml+dumr). */
+__device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl, double sql, double hr, double ur, double vr, double sqr, double sn,
+                                                double cn) {
+  /* sql = sqrt(hl), sqr = sqrt(hr) come from the caller (once per cell, not once per edge) */
   const double g = RDYB_GRAVITY;
-  const double duml = sqrt(hl), dumr = sqrt(hr);
-  const double cl = sqrt(g * hl), cr = sqrt(g * hr);
+  const double duml = sql, dumr = sqr;
+  const double cl = RDYB_SQRT_GRAVITY * sql, cr = RDYB_SQRT_GRAVITY * sqr; /* sqrt(g*h) */
   const double hhat = duml * dumr;
-  const double rsum = 1.0 / (duml + dumr);
+  const double rsum = swe_rcp(duml + dumr);
   const double uhat = (duml * ul + dumr * ur) * rsum;
   const double vhat = (duml * vl + dumr * vr) * rsum;
-  const double chat = sqrt(0.5 * g * (hl + hr));
-  const double rchat = 1.0 / chat;
+  const double c2 = 0.5 * g * (hl + hr);
+  const double rchat = swe_rsqrt(c2);
+  const double chat = c2 * rchat;
   const double uperp = uhat * cn + vhat * sn;
   const double dh = hr - hl, du = ur - ul, dv = vr - vl;
   const double dupar = -du * sn + dv * cn;
@@ -51,9 +89,9 @@ __device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl,
   double a3 = fabs(uperp + chat);
   /* critical flow fix, :55-69 */
   const double da1 = fmax(0.0, 2.0 * ((uperpr - cr) - (uperpl - cl)));
-  if (a1 < da1) a1 = 0.5 * (a1 * a1 / da1 + da1);
+  if (a1 < da1) a1 = 0.5 * (a1 * a1 * swe_rcp(da1) + da1);
   const double da3 = fmax(0.0, 2.0 * ((uperpr + cr) - (uperpl + cl)));
-  if (a3 < da3) a3 = 0.5 * (a3 * a3 / da3 + da3);
+  if (a3 < da3) a3 = 0.5 * (a3 * a3 * swe_rcp(da3) + da3);
   const double t = hhat * duperp * rchat;
   const double w1 = a1 * (0.5 * (dh - t)), w2 = a2 * (hhat * dupar), w3 = a3 * (0.5 * (dh + t));
   const double pl = 0.5 * g * hl * hl, pr = 0.5 * g * hr * hr;
@@ -82,7 +120,7 @@ __device__ __forceinline__ bool swe_critical_outflow_bc(double hl, double ul, do
   if (uperp < 0.0) return false;
   const double q = hl * fabs(uperp);
   hr = cbrt(q * q / RDYB_GRAVITY);
-  const double vel = sqrt(RDYB_GRAVITY * hr);
+  const double vel = swe_sqrt(RDYB_GRAVITY * hr);
   ur = vel * cn;
   vr = vel * sn;
   return true;
@@ -94,14 +132,14 @@ template <int METHOD>
 __device__ __forceinline__ void swe_friction(double h, double hu, double hv, double Fx, double Fy, double bedx, double bedy, double n, double dt,
                                              double xq_thr, double &tbx, double &tby) {
   const double g = RDYB_GRAVITY;
-  const double rh = 1.0 / h;
+  const double rh = swe_rcp(h);
   const double rc = rcbrt(h); /* h^(-1/3) */
   if (METHOD == 0) {
     const double u = hu * rh, v = hv * rh;
     const double Cd = g * (n * n) * rc;
-    const double vel = sqrt(u * u + v * v);
+    const double vel = swe_sqrt(u * u + v * v);
     const double tb = Cd * vel * rh;
-    const double factor = tb / (1.0 + dt * tb);
+    const double factor = tb * swe_rcp(1.0 + dt * tb);
     tbx = (hu + dt * Fx - dt * bedx) * factor;
     tby = (hv + dt * Fy - dt * bedy) * factor;
   } else {
@@ -110,18 +148,18 @@ __device__ __forceinline__ void swe_friction(double h, double hu, double hv, dou
     const double rc2 = rc * rc, rc4 = rc2 * rc2; /* h^(-4/3) */
     const double mxh = mx * rh, myh = my * rh;
     const double gn2 = g * (n * n);
-    const double lambda = gn2 * rc4 * sqrt(mxh * mxh + myh * myh);
+    const double lambda = gn2 * rc4 * swe_sqrt(mxh * mxh + myh * myh);
     double qx, qy;
     if (dt * lambda < xq_thr) {
       qx = mx;
       qy = my;
     } else {
-      const double s = sqrt(1.0 + 4.0 * dt * lambda);
-      const double rd = 1.0 / (-2.0 * dt * lambda);
+      const double s = swe_sqrt(1.0 + 4.0 * dt * lambda);
+      const double rd = -swe_rcp(2.0 * dt * lambda);
       qx = (mx - mx * s) * rd;
       qy = (my - my * s) * rd;
     }
-    const double qmag = sqrt(qx * qx + qy * qy);
+    const double qmag = swe_sqrt(qx * qx + qy * qy);
     const double c = gn2 * (rc4 * rc2 * rc) * qmag; /* g n^2 h^(-7/3) |q| */
     tbx = c * qx;
     tby = c * qy;

@@ -22,7 +22,7 @@
 #define RDYB_TILE_THREADS 256
 
 struct TiledDev {
-  int32_t *tile_cell_begin, *halo_offsets, *halo_cells, *edge_offsets, *edge_bidx;
+  int32_t *tile_cell_begin, *tile_desc, *halo_offsets, *halo_cells, *edge_offsets, *edge_bidx;
   uint32_t *edge_lr;
   double *edge_sn, *edge_cn, *edge_len;
   uint16_t *cell_edges;
@@ -30,6 +30,7 @@ struct TiledDev {
 
 struct TiledArgs {
   SweArgs a;
+  const int32_t *__restrict__ tile_desc;
   const int32_t *__restrict__ tile_cell_begin, *__restrict__ halo_offsets, *__restrict__ halo_cells, *__restrict__ edge_offsets;
   const int32_t *__restrict__ edge_bidx;
   const uint32_t *__restrict__ edge_lr;
@@ -46,12 +47,12 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
   extern __shared__ double smem[];
   const SweArgs &a = p.a;
   const int tile = p.tile0 + blockIdx.x;
-  const int cb = p.tile_cell_begin[tile], ncell = p.tile_cell_begin[tile + 1] - cb;
-  const int ho = p.halo_offsets[tile], nhalo = p.halo_offsets[tile + 1] - ho;
-  const int eo = p.edge_offsets[tile], nedge = p.edge_offsets[tile + 1] - eo;
+  const int4 d0 = *reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tile);
+  const int2 d1 = *reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tile + 4);
+  const int cb = d0.x, ncell = d0.y, eo = d0.z, nedge = d0.w, ho = d1.x, nhalo = d1.y;
   /* shared-memory carve-up */
-  double *sh = smem, *su = sh + p.max_staged, *sv = su + p.max_staged, *sia = sv + p.max_staged;
-  double *sz = sia + p.max_staged; /* HR only */
+  double *sh = smem, *su = sh + p.max_staged, *sv = su + p.max_staged, *sia = sv + p.max_staged, *ssq = sia + p.max_staged;
+  double *sz = ssq + p.max_staged; /* HR only */
   double *shu = sz + (HR ? p.max_staged : 0), *shv = shu + p.max_cells;
   double *sf0 = shv + p.max_cells, *sf1 = sf0 + p.max_edges, *sf2 = sf1 + p.max_edges;
   double *c1l = sf2 + p.max_edges, *c2l = c1l + p.max_edges, *c1r = c2l + p.max_edges, *c2r = c1r + p.max_edges; /* HR only */
@@ -60,11 +61,13 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
   /* ---- phase 1: stage tile cells and halo cells ---- */
   for (int t = threadIdx.x; t < ncell + nhalo; t += RDYB_TILE_THREADS) {
     const int c = t < ncell ? cb + t : p.halo_cells[ho + t - ncell];
+    const int x = t < ncell ? t : p.max_cells + (t - ncell); /* halo cells sit at local index TC + k */
     const double h = a.h[c], hu = a.hu[c], hv = a.hv[c];
     double u, v;
     swe_velocities<HR>(h, hu, hv, tiny, a.ha2, u, v);
-    sh[t] = h; su[t] = u; sv[t] = v; sia[t] = a.inv_area[c];
-    if (HR) sz[t] = a.zc[c];
+    sh[x] = h; su[x] = u; sv[x] = v; sia[x] = a.inv_area[c];
+    if (HR) sz[x] = a.zc[c];
+    else ssq[x] = swe_sqrt(h);
     if (t < ncell) { shu[t] = hu; shv[t] = hv; }
   }
   __syncthreads();
@@ -93,7 +96,8 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
           do_flux = (hls > tiny || hrs > tiny);
         }
         if (do_flux) {
-          f = swe_roe_flux(hl, ul, vl, hr, ur, vr, sn, cn);
+          f = HR ? swe_roe_flux(hl, ul, vl, swe_sqrt(hl), hr, ur, vr, swe_sqrt(hr), sn, cn)
+                 : swe_roe_flux(hl, ul, vl, ssq[l], hr, ur, vr, ssq[r], sn, cn);
           if (COURANT) {
             const double cnum = f.amax * len * fmax(sia[l], sia[r]) * a.dt;
             if (cnum > cmax) { cmax = cnum; carg = (long long)eo + e; }
@@ -117,7 +121,7 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
         ok = swe_critical_outflow_bc(h, ul, vl, sn, cn, hr, ur, vr);
       }
       if (ok && !(h < tiny && hr < tiny)) {
-        f = swe_roe_flux(h, ul, vl, hr, ur, vr, sn, cn);
+        f = swe_roe_flux(h, ul, vl, swe_sqrt(h), hr, ur, vr, swe_sqrt(hr), sn, cn);
         if (COURANT) {
           const double cnum = f.amax * len * sia[l] * a.dt;
           if (cnum > cmax) { cmax = cnum; carg = (long long)eo + e; }
@@ -161,7 +165,7 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
     F2 += -bedy - tby + S2;
     if (a.prim) {
       const bool wet = h >= tiny;
-      const double rr = h / (h * h + a.ha2);
+      const double rr = h * swe_rcp(h * h + a.ha2);
       a.prim[i] = h; a.prim[a.stride + i] = wet ? hu * rr : 0.0; a.prim[2 * a.stride + i] = wet ? hv * rr : 0.0;
     }
     if (EULER) {
@@ -192,7 +196,7 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
 
 /* ---------------- host side ---------------- */
 static inline void tiled_dev_free(TiledDev *d) {
-  void *ptrs[] = {d->tile_cell_begin, d->halo_offsets, d->halo_cells, d->edge_offsets, d->edge_bidx, d->edge_lr, d->edge_sn, d->edge_cn, d->edge_len, d->cell_edges};
+  void *ptrs[] = {d->tile_desc, d->tile_cell_begin, d->halo_offsets, d->halo_cells, d->edge_offsets, d->edge_bidx, d->edge_lr, d->edge_sn, d->edge_cn, d->edge_len, d->cell_edges};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   memset(d, 0, sizeof(*d));
@@ -210,6 +214,7 @@ static inline int tiled_dev_upload(const RdybTiledLayout *T, const RdybLayout *L
   memset(d, 0, sizeof(*d));
   const size_t nt = (size_t)T->num_tiles, ne = (size_t)T->total_edges;
   RDYB_CALL(tiled_up(&d->tile_cell_begin, T->tile_cell_begin, nt + 1));
+  RDYB_CALL(tiled_up(&d->tile_desc, T->tile_desc, 8 * nt));
   RDYB_CALL(tiled_up(&d->halo_offsets, T->halo_offsets, nt + 1));
   RDYB_CALL(tiled_up(&d->halo_cells, T->halo_cells, (size_t)T->total_halo));
   RDYB_CALL(tiled_up(&d->edge_offsets, T->edge_offsets, nt + 1));
@@ -239,7 +244,7 @@ static inline int tiled_launch(const TiledDev &d, const RdybTiledLayout &T, cons
                                bool courant, cudaStream_t stream) {
   TiledArgs p;
   p.a = a;
-  p.tile_cell_begin = d.tile_cell_begin; p.halo_offsets = d.halo_offsets; p.halo_cells = d.halo_cells; p.edge_offsets = d.edge_offsets;
+  p.tile_desc = d.tile_desc; p.tile_cell_begin = d.tile_cell_begin; p.halo_offsets = d.halo_offsets; p.halo_cells = d.halo_cells; p.edge_offsets = d.edge_offsets;
   p.edge_bidx = d.edge_bidx; p.edge_lr = d.edge_lr; p.edge_sn = d.edge_sn; p.edge_cn = d.edge_cn; p.edge_len = d.edge_len;
   p.cell_edges = d.cell_edges;
   const int32_t t0 = a.begin < n_interior ? 0 : T.num_interior_tiles;
@@ -249,7 +254,7 @@ static inline int tiled_launch(const TiledDev &d, const RdybTiledLayout &T, cons
   p.max_cells = T.tile_cells; p.max_staged = T.tile_cells + T.max_halo; p.max_edges = T.max_edges;
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
-  const size_t smem = sizeof(double) * ((size_t)p.max_staged * (hr ? 5 : 4) + 2 * (size_t)p.max_cells + (size_t)p.max_edges * (hr ? 7 : 3));
+  const size_t smem = sizeof(double) * ((size_t)p.max_staged * (hr ? 6 : 5) + 2 * (size_t)p.max_cells + (size_t)p.max_edges * (hr ? 7 : 3));
   RDYB_CHECK(smem <= 227 * 1024, RDYB_ERR_SUP, "tiled kernel: tile needs %zu bytes of shared memory (> 227 KB); use smaller tiles", smem);
   const int nt = t1 - t0;
 #define TL(HRv, SRCv)                                                                                         \

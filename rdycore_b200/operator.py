@@ -13,7 +13,7 @@ import numpy as np
 
 from ._lib import RdybCourantDiagnostics, check, lib
 
-GATHER, TILED = 0, 1
+GATHER, TILED, TILED_ASYNC = 0, 1, 2
 
 
 def _f64(a):
