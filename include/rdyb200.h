@@ -130,7 +130,8 @@ int rdyb_operator_num_local_cells(RdybOperator op, int32_t *n);
  * primitive-variable outputs (src/operator.c:224-299), boundary flux accumulation (swe_petsc.c:623) */
 int rdyb_operator_set_options(RdybOperator op, int courant, int flux_divergence, int primitive_variables, int boundary_fluxes);
 
-/* kernel selection: kind 0 = K1 cell-centric gather (default), 1 = K2 shared-memory tiles of `tile_cells` cells */
+/* kernel selection: kind 0 = K1 cell-centric gather (default), 1 = K2 shared-memory tiles of `tile_cells` cells,
+ * 2 = K3 persistent TMA-staged tiles, 3 = K4 (K3 with compile-time tile shapes for tile_cells 256 or 320; other shapes run K3) */
 int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells);
 
 /* ---- operator data (host arrays in the reference's layouts) ---- */

@@ -20,6 +20,7 @@
 #include "swe_kernels.cuh"
 #include "swe_tiled.cuh"
 #include "swe_tiled_async.cuh"
+#include "swe_tiled_fixed.cuh"
 
 static std::atomic<int64_t> g_launches{0};
 
@@ -103,7 +104,7 @@ struct RdybOperator_ {
   /* tiled-kernel device arrays */
   TiledDev td;
   bool has_tiled = false;
-  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3) */
+  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3) */
   /* options */
   bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
   bool mom_src = false; /* any momentum external source set */
@@ -257,7 +258,7 @@ extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_
 /* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
-  RDYB_CHECK(kind >= 0 && kind <= 2, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
+  RDYB_CHECK(kind >= 0 && kind <= 3, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
   CU(cudaSetDevice(op->device));
   if (kind >= 1) {
     if (op->has_tiled && op->T.tile_cells != tile_cells) {
@@ -457,7 +458,8 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     fill_args(op, t, in, out, dt);
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile, indexed by tile number */
-    if (op->kernel_kind == 2) RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    if (op->kernel_kind == 3 && tiled_fixed_applicable(op->T, op->cfg, t)) RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    else if (op->kernel_kind >= 2) RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     else RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     LAUNCHED();
     CU(cudaGetLastError());

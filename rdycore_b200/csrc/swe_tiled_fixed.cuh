@@ -1,0 +1,382 @@
+/* swe_tiled_fixed.cuh — K4: the persistent warp-specialised TMA tile kernel with a COMPILE-TIME shared-memory layout.
+ *
+ * Same algorithm and device layout as K3 (swe_tiled_async.cuh): per tile, (1) primitive state of the staged cells,
+ * (2) one Roe flux per tile edge, (3) per-cell flux sum + sources + stage update, with a producer warp that stages
+ * tile n+1 through cp.async.bulk (TMA, SASS UBLKCP) + mbarriers while the consumer warps compute tile n.
+ * What changes is everything that the ncu capture of K3 (profiles/r1_ncu_full_swe_tiled_async.txt) showed to be
+ * overhead — 63 % of K3's issued instructions were not fp64 arithmetic:
+ *   - tile capacities (TC cells, HM halo cells, ME edges) are template constants, so every staged array sits at a
+ *     constant offset of one shared-memory struct and loads/stores use immediate offsets (no IMAD address chains,
+ *     no kernel-parameter reloads inside the tile loop);
+ *   - the per-cell flux sum is branch-free: empty slots point at a zero flux entry, the left/right sign is an XOR on
+ *     the high word of 1/area;
+ *   - the producer prefetches the next tiles' descriptors and halo index lists, so its dependent global loads are
+ *     off the critical path of the copy pipeline;
+ *   - the Courant diagnostic keeps max(amax*L/A) and multiplies by dt once at the end.
+ * Meshes whose tiles do not fit the compiled capacities, momentum sources and exotic options fall back to K3.
+ *
+ * Replaces (fused): ApplyInteriorFlux src/swe/swe_petsc.c:215-316, ApplyInteriorFluxHR :1000-1161, ApplyBoundaryFlux
+ * :506-630, ApplySourceSemiImplicit :704-804, ApplySourceImplicitXQ2018 :816-932 and the TSEULER update.
+ */
+#ifndef RDYB_SWE_TILED_FIXED_CUH
+#define RDYB_SWE_TILED_FIXED_CUH
+#include "swe_tiled_async.cuh"
+
+/* one pipeline stage: everything the producer copies for one tile */
+template <int TC, int HM, int ME, bool HR>
+struct alignas(128) FixedStage {
+  static constexpr int CS = TC + HM;
+  double h[CS], hu[CS], hv[CS], ia[CS];
+  double z[HR ? CS : 2];            /* HR: bed elevation of the staged cells */
+  double dzdx[HR ? 2 : TC], dzdy[HR ? 2 : TC];
+  double mann[TC], s0[TC];
+  double esn[ME], ecn[ME], elen[ME];
+  uint32_t elr[ME];
+  uint16_t ce[RDYB_ELL_WIDTH][TC];
+  int32_t desc[8];
+};
+
+/* per-CTA scratch written by the consumers */
+template <int TC, int HM, int ME, bool HR>
+struct alignas(16) FixedScratch {
+  static constexpr int CS = TC + HM;
+  double u[CS], v[CS], sq[HR ? 2 : CS];
+  double f0[ME], f1[ME], f2[ME];
+  double c1l[HR ? ME : 2], c2l[HR ? ME : 2], c1r[HR ? ME : 2], c2r[HR ? ME : 2];
+};
+
+template <int TC, int HM, int ME, bool HR>
+struct FixedSmem {
+  FixedStage<TC, HM, ME, HR> st[2];
+  FixedScratch<TC, HM, ME, HR> sc;
+  uint64_t full_bar[2], empty_bar[2];
+  double wval[16];
+  int wargs[16];
+};
+
+struct FixedArgs {
+  TiledArgs t;
+  int32_t tile_begin, tile_end;
+};
+
+template <int NCONS>
+__device__ __forceinline__ void fixed_consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory"); }
+
+template <int TC, int HM, int ME, int NCONS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+__global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const FixedArgs q) {
+  extern __shared__ __align__(128) char smem_raw[];
+  using Smem = FixedSmem<TC, HM, ME, HR>;
+  Smem &S = *reinterpret_cast<Smem *>(smem_raw);
+  const TiledArgs &p = q.t;
+  const SweArgs &a = p.a;
+  constexpr int HK = (HM + 31) / 32; /* halo indices per producer lane */
+  if (threadIdx.x == 0) {
+    mbar_init(&S.full_bar[0], 33); mbar_init(&S.full_bar[1], 33);
+    mbar_init(&S.empty_bar[0], NCONS); mbar_init(&S.empty_bar[1], NCONS);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    /* the zero flux entry that empty cell-edge slots point at */
+    S.sc.f0[ME - 1] = 0.0; S.sc.f1[ME - 1] = 0.0; S.sc.f2[ME - 1] = 0.0;
+    if (HR) { S.sc.c1l[ME - 1] = 0.0; S.sc.c2l[ME - 1] = 0.0; S.sc.c1r[ME - 1] = 0.0; S.sc.c2r[ME - 1] = 0.0; }
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = gridDim.x;
+
+  if (warp == NCONS / 32) {
+    /* ================= producer warp ================= */
+    int tile = q.tile_begin + blockIdx.x;
+    int4 d0 = make_int4(0, 0, 0, 0), n0 = d0;
+    int2 d1 = make_int2(0, 0), n1 = d1;
+    if (tile < q.tile_end) {
+      d0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tile));
+      d1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tile + 4));
+    }
+    if (tile + G < q.tile_end) {
+      n0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)(tile + G)));
+      n1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)(tile + G) + 4));
+    }
+    int hidx[HK];
+#pragma unroll
+    for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; hidx[k] = t < d1.y ? __ldg(p.halo_cells + d1.x + t) : 0; }
+    for (int it = 0; tile < q.tile_end; tile += G, ++it) {
+      const int s = it & 1;
+      /* prefetch: descriptor two tiles ahead, halo index list one tile ahead */
+      int4 nn0 = make_int4(0, 0, 0, 0);
+      int2 nn1 = make_int2(0, 0);
+      if (tile + 2 * G < q.tile_end) {
+        nn0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)(tile + 2 * G)));
+        nn1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)(tile + 2 * G) + 4));
+      }
+      int nh[HK];
+#pragma unroll
+      for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; nh[k] = t < n1.y ? __ldg(p.halo_cells + n1.x + t) : 0; }
+      mbar_wait(&S.empty_bar[s], ((it >> 1) & 1) ^ 1);
+      auto &st = S.st[s];
+      const int cb = d0.x, ncell = d0.y, eo = d0.z, nedge = d0.w, nhalo = d1.y;
+      uint64_t *bar = &S.full_bar[s];
+      if (lane == 0) {
+        st.desc[0] = cb; st.desc[1] = ncell; st.desc[2] = eo; st.desc[3] = nedge; st.desc[5] = nhalo;
+        const uint32_t bc = (uint32_t)((ncell + 1) & ~1) * 8u; /* per-cell double slices */
+        const uint32_t bh = (uint32_t)((ncell + 7) & ~7) * 2u; /* per-cell uint16 slices */
+        const uint32_t be = (uint32_t)((nedge + 1) & ~1) * 8u; /* per-edge double slices */
+        const uint32_t bl = (uint32_t)((nedge + 3) & ~3) * 4u; /* per-edge uint32 slice */
+        constexpr int ncd = 3 + 1 + (HR ? 1 : 2) + 1 + 1;
+        mbar_expect_tx(bar, bc * ncd + bh * a.width + be * 3 + bl);
+        bulk_g2s(st.h, a.h + cb, bc, bar);
+        bulk_g2s(st.hu, a.hu + cb, bc, bar);
+        bulk_g2s(st.hv, a.hv + cb, bc, bar);
+        bulk_g2s(st.ia, a.inv_area + cb, bc, bar);
+        if (HR) bulk_g2s(st.z, a.zc + cb, bc, bar);
+        else { bulk_g2s(st.dzdx, a.dzdx + cb, bc, bar); bulk_g2s(st.dzdy, a.dzdy + cb, bc, bar); }
+        bulk_g2s(st.mann, a.mann + cb, bc, bar);
+        bulk_g2s(st.s0, a.s0 + cb, bc, bar);
+        for (int k = 0; k < a.width; ++k) bulk_g2s(st.ce[k], p.cell_edges + (size_t)k * a.stride + cb, bh, bar);
+        bulk_g2s(st.esn, p.edge_sn + eo, be, bar);
+        bulk_g2s(st.ecn, p.edge_cn + eo, be, bar);
+        bulk_g2s(st.elen, p.edge_len + eo, be, bar);
+        bulk_g2s(st.elr, p.edge_lr + eo, bl, bar);
+      }
+      /* halo gather: 8-byte async copies straight into the staged arrays at local index TC + t */
+#pragma unroll
+      for (int k = 0; k < HK; ++k) {
+        const int t = lane + 32 * k;
+        if (t < nhalo) {
+          const int c = hidx[k];
+          cp_async8(st.h + TC + t, a.h + c);
+          cp_async8(st.hu + TC + t, a.hu + c);
+          cp_async8(st.hv + TC + t, a.hv + c);
+          cp_async8(st.ia + TC + t, a.inv_area + c);
+          if constexpr (HR) cp_async8(st.z + TC + t, a.zc + c);
+        }
+      }
+      cp_async_arrive_noinc(bar);
+      d0 = n0; d1 = n1; n0 = nn0; n1 = nn1;
+#pragma unroll
+      for (int k = 0; k < HK; ++k) hidx[k] = nh[k];
+    }
+    return;
+  }
+
+  /* ================= consumer warps ================= */
+  auto &sc = S.sc;
+  const double g = RDYB_GRAVITY, tiny = a.tiny_h, ha2 = a.ha2, dt = a.dt;
+  const int tid = threadIdx.x;
+  const int width = a.width;
+  double cmax = 0.0;
+  int carg = -1;
+  int it = 0;
+  for (int tile = q.tile_begin + blockIdx.x; tile < q.tile_end; tile += G, ++it) {
+    const int s = it & 1;
+    mbar_wait(&S.full_bar[s], (it >> 1) & 1);
+    auto &st = S.st[s];
+    const int cb = st.desc[0], ncell = st.desc[1], eo = st.desc[2], nedge = st.desc[3], nhalo = st.desc[5];
+
+    /* ---- phase 1: primitive state of the staged cells: tile cells [0,TC) and halo cells [TC,TC+nhalo) ---- */
+    for (int x = tid; x < TC + nhalo; x += NCONS) {
+      const double h = st.h[x];
+      double u, w;
+      swe_velocities<HR>(h, st.hu[x], st.hv[x], tiny, ha2, u, w);
+      sc.u[x] = u; sc.v[x] = w;
+      if (!HR) sc.sq[x] = swe_sqrt(h);
+    }
+    fixed_consumer_sync<NCONS>();
+
+    /* ---- phase 2: one flux per tile edge ---- */
+    for (int e = tid; e < nedge; e += NCONS) {
+      const uint32_t lr = st.elr[e];
+      const int l = lr & 0xffffu, r = lr >> 16;
+      const double sn = st.esn[e], cn = st.ecn[e], len = st.elen[e];
+      double hl = st.h[l];
+      RoeFlux f = {0.0, 0.0, 0.0, 0.0};
+      double k1l = 0.0, k2l = 0.0, k1r = 0.0, k2r = 0.0;
+      if (r != 0xffff) {
+        double hr = st.h[r];
+        if (!(hl < tiny && hr < tiny)) {
+          const double ul = sc.u[l], vl = sc.v[l], ur = sc.u[r], vr = sc.v[r];
+          bool do_flux = true;
+          double sql, sqr;
+          if (HR) {
+            const double zl = st.z[l], zr = st.z[r], zmax = fmax(zl, zr);
+            const double hls = fmax(0.0, (hl + zl) - zmax), hrs = fmax(0.0, (hr + zr) - zmax);
+            const double corl = 0.5 * g * (hl * hl - hls * hls) * len, corr = 0.5 * g * (hr * hr - hrs * hrs) * len;
+            k1l = corl * cn; k2l = corl * sn; k1r = corr * cn; k2r = corr * sn;
+            hl = hls; hr = hrs;
+            do_flux = (hls > tiny || hrs > tiny);
+            sql = swe_sqrt(hl); sqr = swe_sqrt(hr);
+          } else {
+            sql = sc.sq[l]; sqr = sc.sq[r];
+          }
+          if (do_flux) {
+            f = swe_roe_flux(hl, ul, vl, sql, hr, ur, vr, sqr, sn, cn);
+            if (COURANT) {
+              const double cnum = f.amax * len * fmax(st.ia[l], st.ia[r]);
+              if (cnum > cmax) { cmax = cnum; carg = eo + e; }
+            }
+          }
+        }
+      } else {
+        /* boundary edge (rare): ApplyBoundaryFlux, src/swe/swe_petsc.c:506-630 */
+        const int j = p.edge_bidx[eo + e];
+        const double h = hl;
+        double ul, vl;
+        swe_velocities<false>(h, st.hu[l], st.hv[l], tiny, ha2, ul, vl);
+        double hr = 0.0, ur = 0.0, vr = 0.0;
+        bool ok = true;
+        const int type = a.btype[j];
+        if (type == RDYB_CONDITION_DIRICHLET) {
+          hr = a.bval[j];
+          swe_velocities<false>(hr, a.bval[a.nbe + j], a.bval[2 * a.nbe + j], tiny, ha2, ur, vr);
+        } else if (type == RDYB_CONDITION_REFLECTING) {
+          swe_reflecting_bc(h, ul, vl, sn, cn, hr, ur, vr);
+        } else {
+          ok = swe_critical_outflow_bc(h, ul, vl, sn, cn, hr, ur, vr);
+        }
+        if (ok && !(h < tiny && hr < tiny)) {
+          f = swe_roe_flux(h, ul, vl, swe_sqrt(h), hr, ur, vr, swe_sqrt(hr), sn, cn);
+          if (COURANT) {
+            const double cnum = f.amax * len * st.ia[l];
+            if (cnum > cmax) { cmax = cnum; carg = eo + e; }
+          }
+        }
+        if (a.bflux) {
+          a.bflux[j] = f.f0; a.bflux[a.nbe + j] = f.f1; a.bflux[2 * a.nbe + j] = f.f2;
+          a.bacc[j] += dt * f.f0; a.bacc[a.nbe + j] += dt * f.f1; a.bacc[2 * a.nbe + j] += dt * f.f2;
+        }
+      }
+      sc.f0[e] = f.f0 * len; sc.f1[e] = f.f1 * len; sc.f2[e] = f.f2 * len;
+      if (HR) { sc.c1l[e] = k1l; sc.c2l[e] = k2l; sc.c1r[e] = k1r; sc.c2r[e] = k2r; }
+    }
+    fixed_consumer_sync<NCONS>();
+
+    /* ---- phase 3: per-cell flux sum (branch-free), sources, update ---- */
+    for (int t = tid; t < ncell; t += NCONS) {
+      const int i = cb + t;
+      const double h = st.h[t], hu = st.hu[t], hv = st.hv[t], ia = st.ia[t];
+      const int ia_hi = __double2hiint(ia), ia_lo = __double2loint(ia);
+      double F0 = 0.0, F1 = 0.0, F2 = 0.0;
+#pragma unroll
+      for (int k = 0; k < RDYB_ELL_WIDTH; ++k) {
+        if (k < width) {
+          const uint32_t ce = st.ce[k][t];
+          const int e = min((int)(ce & 0x7fffu), ME - 1);                  /* empty slot (0xffff) -> the zero flux entry */
+          const int flip = (int)((~ce & 0x8000u) << 16);                   /* left cell: -1/area, right cell: +1/area */
+          const double sgn = __hiloint2double(ia_hi ^ flip, ia_lo);
+          F0 = fma(sc.f0[e], sgn, F0); F1 = fma(sc.f1[e], sgn, F1); F2 = fma(sc.f2[e], sgn, F2);
+          if (HR) {
+            const bool right = (ce & 0x8000u) != 0;
+            F1 = fma(right ? sc.c1r[e] : sc.c1l[e], sgn, F1);
+            F2 = fma(right ? sc.c2r[e] : sc.c2l[e], sgn, F2);
+          }
+        }
+      }
+      if (a.fdiv) { a.fdiv[i] = F0; a.fdiv[a.stride + i] = F1; a.fdiv[2 * a.stride + i] = F2; }
+      double bedx = 0.0, bedy = 0.0, tbx = 0.0, tby = 0.0;
+      if (!HR) { bedx = st.dzdx[t] * g * h; bedy = st.dzdy[t] * g * h; }
+      if (h >= tiny) swe_friction<SRC>(h, hu, hv, F1, F2, bedx, bedy, st.mann[t], dt, a.xq_thr, tbx, tby);
+      F0 += st.s0[t];
+      F1 += -bedx - tbx;
+      F2 += -bedy - tby;
+      if (a.prim) {
+        const bool wet = h >= tiny;
+        const double rr = h * swe_rcp(h * h + ha2);
+        a.prim[i] = h; a.prim[a.stride + i] = wet ? hu * rr : 0.0; a.prim[2 * a.stride + i] = wet ? hv * rr : 0.0;
+      }
+      if (EULER) { a.o0[i] = h + dt * F0; a.o1[i] = hu + dt * F1; a.o2[i] = hv + dt * F2; }
+      else { a.o0[i] = F0; a.o1[i] = F1; a.o2[i] = F2; }
+    }
+    mbar_arrive(&S.empty_bar[s]); /* this thread is done reading stage s */
+  }
+
+  if (COURANT && a.cmax) {
+    cmax *= dt;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const double ov = __shfl_down_sync(0xffffffffu, cmax, off);
+      const int oa = __shfl_down_sync(0xffffffffu, carg, off);
+      if (ov > cmax || (ov == cmax && oa >= 0 && (carg < 0 || oa < carg))) { cmax = ov; carg = oa; }
+    }
+    if (lane == 0) { S.wval[warp] = cmax; S.wargs[warp] = carg; }
+    fixed_consumer_sync<NCONS>();
+    if (tid == 0) {
+      for (int w = 1; w < NCONS / 32; ++w)
+        if (S.wval[w] > cmax || (S.wval[w] == cmax && S.wargs[w] >= 0 && (carg < 0 || S.wargs[w] < carg))) { cmax = S.wval[w]; carg = S.wargs[w]; }
+      const int slot = q.tile_begin + blockIdx.x; /* tile numbers of different launches do not overlap, so neither do the slots */
+      const long long arg = carg;
+      if (cmax > a.cmax[slot] || (cmax == a.cmax[slot] && arg >= 0 && (a.carg[slot] < 0 || arg < a.carg[slot]))) { a.cmax[slot] = cmax; a.carg[slot] = arg; }
+    }
+  }
+}
+
+/* ---------------- host side ---------------- */
+template <int TC, int HM, int ME, int NCONS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
+  static bool configured = false;
+  static int blocks_per_sm = 0, num_sms = 0;
+  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, MINB, HR, SRC, EULER, COURANT>;
+  const size_t smem = sizeof(FixedSmem<TC, HM, ME, HR>);
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "fixed tile kernel: %zu bytes of shared memory per CTA not available (%s)", smem, cudaGetErrorString(e));
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NCONS + 32, smem);
+    if (e != cudaSuccess || blocks_per_sm < 1) return rdyb_fail(RDYB_ERR_CUDA, "fixed tile kernel does not fit on an SM with %zu bytes of shared memory", smem);
+    configured = true;
+  }
+  const char *env = getenv("RDYB_CTAS_PER_SM");
+  int bps = blocks_per_sm;
+  if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
+  int grid = num_sms * bps;
+  if (grid > ntiles) grid = ntiles;
+  kern<<<grid, NCONS + 32, smem, stream>>>(q);
+  return RDYB_SUCCESS;
+}
+
+template <int TC, int HM, int ME, int NCONS, int MINB, bool HR>
+static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
+#define FL(SRCv)                                                                                                                   \
+  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, true, true>(q, nt, stream)                                  \
+                    : fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, true, false>(q, nt, stream))                                \
+         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, false, true>(q, nt, stream)                                 \
+                    : fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, false, false>(q, nt, stream)))
+  return xq ? FL(1) : FL(0);
+#undef FL
+}
+
+/* the compiled tile shapes: {tile cells, halo capacity, edge capacity (one entry is the zero flux), consumer threads, CTAs/SM} */
+#define RDYB_FIXED_A 256, 96, 576, 256, 2 /* triangles, quads and mixed meshes */
+#define RDYB_FIXED_B 320, 96, 544, 256, 2 /* triangle meshes: ~1.6 edges per cell fill two full passes of 256 threads */
+#define RDYB_FIXED_C 256, 96, 448, 256, 2 /* hydrostatic reconstruction on triangle meshes */
+
+/* true when K4 has a compiled shape for this layout and option set */
+static inline bool tiled_fixed_applicable(const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a) {
+  if (a.s1 || a.s2) return false; /* momentum sources: K3 */
+  if (T.max_halo > 96) return false;
+  const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
+  if (hr) return T.tile_cells == 256 && T.max_edges <= 447;
+  if (T.tile_cells == 256) return T.max_edges <= 575;
+  if (T.tile_cells == 320) return T.max_edges <= 543;
+  return false;
+}
+
+static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a, int32_t n_interior,
+                                     bool euler, bool courant, cudaStream_t stream) {
+  FixedArgs q;
+  TiledArgs &p = q.t;
+  p.a = a;
+  p.tile_desc = d.tile_desc; p.tile_cell_begin = d.tile_cell_begin; p.halo_offsets = d.halo_offsets; p.halo_cells = d.halo_cells;
+  p.edge_offsets = d.edge_offsets; p.edge_bidx = d.edge_bidx; p.edge_lr = d.edge_lr; p.edge_sn = d.edge_sn; p.edge_cn = d.edge_cn;
+  p.edge_len = d.edge_len; p.cell_edges = d.cell_edges;
+  p.tile0 = 0; p.max_cells = T.tile_cells; p.max_staged = 0; p.max_edges = 0;
+  q.tile_begin = a.begin < n_interior ? 0 : T.num_interior_tiles;
+  q.tile_end = (a.end <= n_interior && a.begin < n_interior) ? T.num_interior_tiles : T.num_tiles;
+  if (q.tile_end <= q.tile_begin) return RDYB_SUCCESS;
+  const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
+  const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
+  const int nt = q.tile_end - q.tile_begin;
+  if (hr) return fixed_launch_cfg<RDYB_FIXED_C, true>(q, nt, xq, euler, courant, stream);
+  if (T.tile_cells == 320) return fixed_launch_cfg<RDYB_FIXED_B, false>(q, nt, xq, euler, courant, stream);
+  return fixed_launch_cfg<RDYB_FIXED_A, false>(q, nt, xq, euler, courant, stream);
+}
+#endif
