@@ -130,7 +130,7 @@ int rdyb_layout_build(const RdybMeshView *mv, int32_t nb, const RdybBoundaryView
     }
     /* the last (< 8) interior cells are treated as frontier so that both ranges start on a multiple of 8 cells
      * (16-byte alignment of every per-cell slice a tile fetches with a bulk async copy) */
-    if (L->n_interior < N) L->n_interior &= ~7;
+    if (L->n_interior < N) L->n_interior &= ~15; /* 16-byte aligned slices of the per-cell uint8 / uint16 / double arrays for bulk copies */
   }
   /* ghosts: per peer in recv order, then the remaining non-owned cells in ascending local id */
   {

@@ -66,8 +66,9 @@ __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, d
 /* ComputeSWERoeEigenspectrum + the flux loop of ComputeSWERoeFlux, src/swe/swe_roe_flux_petsc.h:15-81, 108-128.
  * Inputs are (h,u,v,sqrt h) of the left and right state and the edge normal (cn,sn).  At least one of hl,hr must be > 0.
  * Re-association vs the reference: sqrt(g h) = sqrt(g) sqrt(h); chat and 1/chat from one rsqrt; one shared 1/(duml+dumr). */
-__device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl, double sql, double hr, double ur, double vr, double sqr, double sn,
-                                                double cn) {
+template <bool FIX>
+__device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double vl, double sql, double hr, double ur, double vr, double sqr, double sn,
+                                                  double cn, bool &needfix) {
   /* sql = sqrt(hl), sqr = sqrt(hr) come from the caller (once per cell, not once per edge) */
   const double g = RDYB_GRAVITY;
   const double duml = sql, dumr = sqr;
@@ -89,9 +90,14 @@ __device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl,
   double a3 = fabs(uperp + chat);
   /* critical flow fix, :55-69 */
   const double da1 = fmax(0.0, 2.0 * ((uperpr - cr) - (uperpl - cl)));
-  if (a1 < da1) a1 = 0.5 * (a1 * a1 * swe_rcp(da1) + da1);
   const double da3 = fmax(0.0, 2.0 * ((uperpr + cr) - (uperpl + cl)));
-  if (a3 < da3) a3 = 0.5 * (a3 * a3 * swe_rcp(da3) + da3);
+  if (FIX) {
+    if (a1 < da1) a1 = 0.5 * (a1 * a1 * swe_rcp(da1) + da1);
+    if (a3 < da3) a3 = 0.5 * (a3 * a3 * swe_rcp(da3) + da3);
+    needfix = false;
+  } else {
+    needfix = (a1 < da1) || (a3 < da3); /* the caller re-evaluates these (rare) edges with FIX = true */
+  }
   const double t = hhat * duperp * rchat;
   const double w1 = a1 * (0.5 * (dh - t)), w2 = a2 * (hhat * dupar), w3 = a3 * (0.5 * (dh + t));
   const double pl = 0.5 * g * hl * hl, pr = 0.5 * g * hr * hr;
@@ -103,6 +109,11 @@ __device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl,
   F.f2 = 0.5 * ((vl * ql + pl * sn) + (vr * qr + pr * sn) - (vhat - chat * sn) * w1 - cn * w2 - (vhat + chat * sn) * w3);
   F.amax = chat + fabs(uperp);
   return F;
+}
+__device__ __forceinline__ RoeFlux swe_roe_flux(double hl, double ul, double vl, double sql, double hr, double ur, double vr, double sqr, double sn,
+                                                double cn) {
+  bool unused;
+  return swe_roe_flux_t<true>(hl, ul, vl, sql, hr, ur, vr, sqr, sn, cn, unused);
 }
 
 /* ApplyReflectingBC, src/swe/swe_petsc.c:434-461 (acts on velocities) */
