@@ -21,6 +21,7 @@
 #include "swe_tiled.cuh"
 #include "swe_tiled_async.cuh"
 #include "swe_tiled_fixed.cuh"
+#include "swe_warp.cuh"
 
 static std::atomic<int64_t> g_launches{0};
 
@@ -104,7 +105,12 @@ struct RdybOperator_ {
   /* tiled-kernel device arrays */
   TiledDev td;
   bool has_tiled = false;
-  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3) */
+  /* warp-tile kernel (K5) */
+  RdybWarpLayout WL;
+  WarpDev wd;
+  bool has_warp = false, warp_used = false; /* warp_used: the last launch ran K5 (not a fallback) */
+  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3),
+                          4 = one 32-cell mini-tile per warp (K5; falls back to K4 / K3) */
   /* options */
   bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
   bool mom_src = false; /* any momentum external source set */
@@ -146,6 +152,8 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   for (void *p : ptrs)
     if (p) cudaFree(p);
   tiled_dev_free(&op->td);
+  warp_dev_free(&op->wd);
+  rdyb_warp_layout_free(&op->WL);
   if (op->ev_pack) cudaEventDestroy(op->ev_pack);
   if (op->ev_halo) cudaEventDestroy(op->ev_halo);
   if (op->ev_t0) cudaEventDestroy(op->ev_t0);
@@ -224,6 +232,8 @@ extern "C" int rdyb_operator_create(const RdybConfig *config, const RdybMeshView
   memset(&op->L, 0, sizeof(op->L));
   memset(&op->T, 0, sizeof(op->T));
   memset(&op->td, 0, sizeof(op->td));
+  memset(&op->WL, 0, sizeof(op->WL));
+  memset(&op->wd, 0, sizeof(op->wd));
   int ierr = operator_create_impl(op, config, mesh, nb, bnd, halo, device, cuda_stream);
   if (ierr) {
     char saved[1024];
@@ -258,7 +268,7 @@ extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_
 /* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
-  RDYB_CHECK(kind >= 0 && kind <= 3, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
+  RDYB_CHECK(kind >= 0 && kind <= 4, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
   CU(cudaSetDevice(op->device));
   if (kind >= 1) {
     if (op->has_tiled && op->T.tile_cells != tile_cells) {
@@ -270,6 +280,18 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
       RDYB_CALL(rdyb_tiled_layout_build(&op->L, tile_cells, &op->T));
       RDYB_CALL(tiled_dev_upload(&op->T, &op->L, &op->td));
       op->has_tiled = true;
+    }
+  }
+  if (kind == 4) {
+    if (op->has_warp && op->WL.tile_cells != tile_cells) {
+      warp_dev_free(&op->wd);
+      rdyb_warp_layout_free(&op->WL);
+      op->has_warp = false;
+    }
+    if (!op->has_warp) {
+      RDYB_CALL(rdyb_warp_layout_build(&op->L, tile_cells, &op->WL));
+      RDYB_CALL(warp_dev_upload(&op->WL, &op->L, &op->wd));
+      op->has_warp = true;
     }
   }
   op->kernel_kind = kind;
@@ -458,7 +480,9 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     fill_args(op, t, in, out, dt);
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile, indexed by tile number */
-    if (op->kernel_kind == 3 && tiled_fixed_applicable(op->T, op->cfg, t)) RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    op->warp_used = op->kernel_kind == 4 && op->has_warp && warp_applicable(op->WL, t);
+    if (op->warp_used) RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T, op->cfg, t)) RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     else if (op->kernel_kind >= 2) RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     else RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     LAUNCHED();
@@ -665,7 +689,11 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   long long arg = -1;
   for (size_t i = 0; i < v.size(); ++i)
     if (v[i] > d->max_courant_num || (v[i] == d->max_courant_num && a[i] >= 0 && (arg < 0 || a[i] < arg))) { d->max_courant_num = v[i]; arg = a[i]; }
-  if (arg >= 0 && op->kernel_kind >= 1 && op->has_tiled) {
+  if (arg >= 0 && op->kernel_kind == 4 && op->has_warp && op->warp_used) {
+    /* warp kernel: arg = global mini-tile-edge index */
+    d->global_edge_id = op->WL.edge_id[arg];
+    d->global_cell_id = op->L.dev_to_local[op->WL.edge_cell[arg]];
+  } else if (arg >= 0 && op->kernel_kind >= 1 && op->has_tiled) {
     /* tiled kernel: arg = global tile-edge index */
     d->global_edge_id = op->T.edge_id[arg];
     d->global_cell_id = op->L.dev_to_local[op->T.edge_cell[arg]];

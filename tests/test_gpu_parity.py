@@ -9,13 +9,13 @@ import pytest
 
 from rdycore_b200 import cases
 from rdycore_b200.mesh import HostMesh
-from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, Operator
+from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, Operator
 
 from util import REL_TOL, assert_state_close, make_oracle, state_error
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED]
+KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP]
 
 
 def _op(case, kernel=GATHER, **opts):
