@@ -22,6 +22,10 @@
 
 #include "swe_tiled_fixed.cuh"
 
+#ifndef RDYB_WARP_ILP
+#define RDYB_WARP_ILP 1
+#endif
+
 struct WarpDev {
   int32_t *tile_desc, *halo_cells, *edge_bidx;
   uint16_t *wdesc, *whalo, *edge_lr;
@@ -64,27 +68,29 @@ struct alignas(16) WarpScratch {
   double f1r[HR ? EC : 2], f2r[HR ? EC : 2]; /* HR: momentum flux + pressure correction as seen by the right cell (f1, f2: by the left cell) */
 };
 
-template <int TC, int HM, int ME, int WH, int EC, bool HR>
+template <int TC, int HM, int ME, int WH, int EC, int NS, int NWC, bool HR>
 struct WarpSmem {
-  WarpStage<TC, HM, ME, WH, HR> st[2];
-  WarpScratch<EC, HR> ws[TC / 32];
-  uint64_t full_bar[2], empty_bar[2];
-  double wval[TC / 32];
-  int wargs[TC / 32];
+  WarpStage<TC, HM, ME, WH, HR> st[NS]; /* NS-deep pipeline of staged tiles */
+  WarpScratch<EC, HR> ws[NWC];          /* one scratch per consumer warp */
+  uint64_t full_bar[NS], empty_bar[NS];
+  double wval[NWC];
+  int wargs[NWC];
+  int claim;                            /* next unclaimed (tile, mini-tile) work item of this CTA */
 };
 
-template <int TC, int HM, int ME, int WH, int EC, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
-__global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs p) {
+template <int TC, int HM, int ME, int WH, int EC, int NS, int NWC, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+__global__ void __launch_bounds__(NWC * 32 + 32, MINB) swe_warp_kernel(const WarpArgs p) {
   extern __shared__ __align__(128) char smem_raw[];
-  using Smem = WarpSmem<TC, HM, ME, WH, EC, HR>;
+  using Smem = WarpSmem<TC, HM, ME, WH, EC, NS, NWC, HR>;
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const SweArgs &a = p.a;
-  constexpr int NW = TC / 32;        /* consumer warps */
+  constexpr int NW = NWC;            /* consumer warps */
+  constexpr int NMT = TC / 32;       /* mini-tiles per staged tile */
   constexpr int HK = (HM + 31) / 32; /* halo indices per producer lane */
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    mbar_init(&S.full_bar[0], 33); mbar_init(&S.full_bar[1], 33);
-    mbar_init(&S.empty_bar[0], TC); mbar_init(&S.empty_bar[1], TC);
+    for (int s = 0; s < NS; ++s) { mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], TC); }
+    S.claim = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp < NW && lane == 0) {
@@ -112,7 +118,7 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
 #pragma unroll
     for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; hidx[k] = t < d1.y ? __ldg(p.halo_cells + d1.x + t) : 0; }
     for (int it = 0; tile < p.tile_end; tile += G, ++it) {
-      const int s = it & 1;
+      const int s = it % NS;
       /* prefetch: descriptor two tiles ahead, halo index list one tile ahead */
       int4 nn0 = zero4, nn1 = zero4;
       if (tile + 2 * G < p.tile_end) {
@@ -122,7 +128,7 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
       int nh[HK];
 #pragma unroll
       for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; nh[k] = t < n1.y ? __ldg(p.halo_cells + n1.x + t) : 0; }
-      mbar_wait(&S.empty_bar[s], ((it >> 1) & 1) ^ 1);
+      mbar_wait(&S.empty_bar[s], ((it / NS) & 1) ^ 1);
       auto &st = S.st[s];
       const int cb = d0.x, ncell = d0.y, eo = d0.z, nedge = d0.w, nhalo = d1.y, wo = d1.z, nwh = d1.w;
       uint64_t *bar = &S.full_bar[s];
@@ -133,7 +139,7 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
         const uint32_t be = (uint32_t)((nedge + 1) & ~1) * 8u;  /* per-edge double slices */
         const uint32_t bl = (uint32_t)((nedge + 7) & ~7) * 2u;  /* per-edge uint16 slice */
         const uint32_t bw = (uint32_t)((nwh + 7) & ~7) * 2u;    /* mini-tile halo lists */
-        constexpr uint32_t bd = NW * 8u;                        /* mini-tile descriptors */
+        constexpr uint32_t bd = NMT * 8u;                       /* mini-tile descriptors */
         constexpr int ncd = 3 + 1 + (HR ? 1 : 2) + 1 + 1;
         mbar_expect_tx(bar, bc * ncd + b8 * a.width + be * 3 + bl + bw + bd);
         bulk_g2s(st.h, a.h + cb, bc, bar);
@@ -150,7 +156,7 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
         bulk_g2s(st.elen, p.edge_len + eo, be, bar);
         bulk_g2s(st.elr, p.edge_lr + eo, bl, bar);
         if (bw) bulk_g2s(st.whalo, p.whalo + wo, bw, bar);
-        bulk_g2s(st.wdesc, p.wdesc + (size_t)tile * (NW * 4), bd, bar);
+        bulk_g2s(st.wdesc, p.wdesc + (size_t)tile * (NMT * 4), bd, bar);
       }
       /* halo gather: 8-byte async copies straight into the staged arrays at local index TC + t */
 #pragma unroll
@@ -173,21 +179,27 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
     return;
   }
 
-  /* ================= consumer warps: one 32-cell mini-tile each ================= */
+  /* ================= consumer warps: claim (tile, mini-tile) work items in order, one 32-cell mini-tile at a time ================= */
   auto &ws = S.ws[warp];
   const double g = RDYB_GRAVITY, tiny = a.tiny_h, ha2 = a.ha2, dt = a.dt;
   const int width = a.width;
   double cmax = 0.0;
   int carg = -1;
-  int it = 0;
-  for (int tile = p.tile_begin + blockIdx.x; tile < p.tile_end; tile += G, ++it) {
-    const int s = it & 1;
-    mbar_wait(&S.full_bar[s], (it >> 1) & 1);
+  const int my_tiles = (p.tile_end - p.tile_begin - (int)blockIdx.x + G - 1) / G; /* tiles this CTA walks */
+  const int nitems = my_tiles * NMT;
+  for (;;) {
+    int item = 0;
+    if (lane == 0) item = atomicAdd(&S.claim, 1);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= nitems) break;
+    const int it = item / NMT, mt = item - it * NMT;
+    const int s = it % NS;
+    mbar_wait(&S.full_bar[s], (it / NS) & 1);
     auto &st = S.st[s];
     const int cb = st.desc[0], ncell = st.desc[1], eo = st.desc[2];
-    const uint2 wdp = *reinterpret_cast<const uint2 *>(&st.wdesc[4 * warp]);
+    const uint2 wdp = *reinterpret_cast<const uint2 *>(&st.wdesc[4 * mt]);
     const int ebeg = wdp.x & 0xffffu, nint = (wdp.x >> 16) & 0xffu, nbnd = wdp.x >> 24, hbeg = wdp.y & 0xffffu, nwh = wdp.y >> 16;
-    const int t = 32 * warp + lane; /* this lane's cell within the tile */
+    const int t = 32 * mt + lane; /* this lane's cell within the tile */
 
     /* ---- phase 1: primitive state of the lane's own cell and of one outside cell of the mini-tile ---- */
     {
@@ -232,6 +244,7 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
       o0 = f0; o1l = f1 + k1l; o2l = f2 + k2l; o1r = f1 + k1r; o2r = f2 + k2r;
       cnum = ok ? f.amax * len * fmax(ws.ia[l], ws.ia[r]) : 0.0;
     };
+#if RDYB_WARP_ILP == 2
     for (int base = 0; base < nint; base += 64) {
       const int ea = base + lane, eb = ea + 32;
       const bool va = ea < nint, vb = eb < nint;
@@ -258,9 +271,25 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
         if (bc > cmax) { cmax = bc; carg = eo + ebeg + eb; }
       }
     }
+#else
+    for (int ea = lane; ea < nint; ea += 32) {
+      double a0, a1l, a2l, a1r, a2r, ac;
+      bool nfa;
+      edge_flux(std::false_type{}, ea, true, a0, a1l, a2l, a1r, a2r, ac, nfa);
+      if (__any_sync(__activemask(), nfa)) { /* critical-flow fix needed somewhere in the warp (rare): redo those edges */
+        bool dummy;
+        if (nfa) edge_flux(std::true_type{}, ea, true, a0, a1l, a2l, a1r, a2r, ac, dummy);
+      }
+      ws.f0[ea] = a0; ws.f1[ea] = a1l; ws.f2[ea] = a2l;
+      if (HR) { ws.f1r[ea] = a1r; ws.f2r[ea] = a2r; }
+      if (COURANT) {
+        if (ac > cmax) { cmax = ac; carg = eo + ebeg + ea; }
+      }
+    }
+#endif
     /* boundary edges of the mini-tile (rare): ApplyBoundaryFlux, src/swe/swe_petsc.c:506-630 */
     for (int e = nint + lane; e < nint + nbnd; e += 32) {
-      const int l = st.elr[ebeg + e] & 0xffu, xl = 32 * warp + l;
+      const int l = st.elr[ebeg + e] & 0xffu, xl = 32 * mt + l;
       const double sn = st.esn[ebeg + e], cn = st.ecn[ebeg + e], len = st.elen[ebeg + e];
       const int j = p.edge_bidx[eo + ebeg + e];
       const double h = ws.h[l];
@@ -345,7 +374,7 @@ __global__ void __launch_bounds__(TC + 32, MINB) swe_warp_kernel(const WarpArgs 
       if (ov > cmax || (ov == cmax && oa >= 0 && (carg < 0 || oa < carg))) { cmax = ov; carg = oa; }
     }
     if (lane == 0) { S.wval[warp] = cmax; S.wargs[warp] = carg; }
-    asm volatile("bar.sync 1, %0;" ::"n"(TC) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(NWC * 32) : "memory");
     if (threadIdx.x == 0) {
       for (int w = 1; w < NW; ++w)
         if (S.wval[w] > cmax || (S.wval[w] == cmax && S.wargs[w] >= 0 && (carg < 0 || S.wargs[w] < carg))) { cmax = S.wval[w]; carg = S.wargs[w]; }
@@ -390,13 +419,13 @@ static inline int warp_dev_upload(const RdybWarpLayout *W, const RdybLayout *L, 
   return RDYB_SUCCESS;
 }
 
-template <int TC, int HM, int ME, int WH, int EC, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+template <int TC, int HM, int ME, int WH, int EC, int NS, int NWC, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
 static int warp_launch_t(const WarpArgs &q, int ntiles, cudaStream_t stream) {
   static bool configured = false;
   static int blocks_per_sm = 0, num_sms = 0;
-  using Smem = WarpSmem<TC, HM, ME, WH, EC, HR>;
+  using Smem = WarpSmem<TC, HM, ME, WH, EC, NS, NWC, HR>;
   static_assert(ME % 8 == 0 && WH % 8 == 0 && TC % 64 == 0 && HM % 2 == 0, "bulk-copy alignment of the staged slices");
-  auto kern = swe_warp_kernel<TC, HM, ME, WH, EC, MINB, HR, SRC, EULER, COURANT>;
+  auto kern = swe_warp_kernel<TC, HM, ME, WH, EC, NS, NWC, MINB, HR, SRC, EULER, COURANT>;
   const size_t smem = sizeof(Smem);
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -404,7 +433,7 @@ static int warp_launch_t(const WarpArgs &q, int ntiles, cudaStream_t stream) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, TC + 32, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NWC * 32 + 32, smem);
     if (e != cudaSuccess || blocks_per_sm < 1) return rdyb_fail(RDYB_ERR_CUDA, "warp tile kernel does not fit on an SM with %zu bytes of shared memory", smem);
     configured = true;
   }
@@ -413,27 +442,32 @@ static int warp_launch_t(const WarpArgs &q, int ntiles, cudaStream_t stream) {
   if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
   int grid = num_sms * bps;
   if (grid > ntiles) grid = ntiles;
-  kern<<<grid, TC + 32, smem, stream>>>(q);
+  kern<<<grid, NWC * 32 + 32, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }
 
-template <int TC, int HM, int ME, int WH, int EC, int MINB, bool HR>
+template <int TC, int HM, int ME, int WH, int EC, int NS, int NWC, int MINB, bool HR>
 static int warp_launch_cfg(const WarpArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
 #define WLC(SRCv)                                                                                                        \
-  (euler ? (courant ? warp_launch_t<TC, HM, ME, WH, EC, MINB, HR, SRCv, true, true>(q, nt, stream)                        \
-                    : warp_launch_t<TC, HM, ME, WH, EC, MINB, HR, SRCv, true, false>(q, nt, stream))                      \
-         : (courant ? warp_launch_t<TC, HM, ME, WH, EC, MINB, HR, SRCv, false, true>(q, nt, stream)                       \
-                    : warp_launch_t<TC, HM, ME, WH, EC, MINB, HR, SRCv, false, false>(q, nt, stream)))
+  (euler ? (courant ? warp_launch_t<TC, HM, ME, WH, EC, NS, NWC, MINB, HR, SRCv, true, true>(q, nt, stream)                        \
+                    : warp_launch_t<TC, HM, ME, WH, EC, NS, NWC, MINB, HR, SRCv, true, false>(q, nt, stream))                      \
+         : (courant ? warp_launch_t<TC, HM, ME, WH, EC, NS, NWC, MINB, HR, SRCv, false, true>(q, nt, stream)                       \
+                    : warp_launch_t<TC, HM, ME, WH, EC, NS, NWC, MINB, HR, SRCv, false, false>(q, nt, stream)))
   return xq ? WLC(1) : WLC(0);
 #undef WLC
 }
 
-/* compiled shape: {tile cells, tile halo capacity, tile edge capacity, tile mini-halo capacity, mini-tile edge capacity, CTAs/SM} */
-#define RDYB_WARP_SHAPE 256, 96, 544, 256, 96, 2
+/* compiled shapes: {tile cells, tile halo capacity, tile edge capacity, tile mini-halo capacity, mini-tile edge capacity,
+ * pipeline stages, consumer warps, CTAs/SM} */
+#define RDYB_WARP_SHAPE_256 256, 96, 544, 256, 96, 2, 8, 2
+#define RDYB_WARP_SHAPE_128 128, 64, 288, 128, 80, 4, 8, 2
 
+static inline bool warp_shape_fits(const RdybWarpLayout &W, int tc, int hm, int me, int wh, int ec) {
+  return W.tile_cells == tc && W.max_halo <= hm && W.max_tile_edges <= me && W.max_tile_whalo <= wh && W.max_warp_edges <= ec - 1 && W.max_warp_halo <= 32;
+}
 static inline bool warp_applicable(const RdybWarpLayout &W, const SweArgs &a) {
   if (a.s1 || a.s2) return false; /* momentum sources: K3 */
-  return W.tile_cells == 256 && W.max_halo <= 96 && W.max_tile_edges <= 544 && W.max_tile_whalo <= 256 && W.max_warp_edges <= 95 && W.max_warp_halo <= 32;
+  return warp_shape_fits(W, 256, 96, 544, 256, 96) || warp_shape_fits(W, 128, 64, 288, 128, 80);
 }
 
 static inline int warp_launch(const WarpDev &d, const RdybWarpLayout &W, const RdybConfig &cfg, const SweArgs &a, int32_t n_interior, bool euler,
@@ -448,7 +482,11 @@ static inline int warp_launch(const WarpDev &d, const RdybWarpLayout &W, const R
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
   const int nt = q.tile_end - q.tile_begin;
-  if (hr) return warp_launch_cfg<RDYB_WARP_SHAPE, true>(q, nt, xq, euler, courant, stream);
-  return warp_launch_cfg<RDYB_WARP_SHAPE, false>(q, nt, xq, euler, courant, stream);
+  if (W.tile_cells == 128) {
+    if (hr) return warp_launch_cfg<RDYB_WARP_SHAPE_128, true>(q, nt, xq, euler, courant, stream);
+    return warp_launch_cfg<RDYB_WARP_SHAPE_128, false>(q, nt, xq, euler, courant, stream);
+  }
+  if (hr) return warp_launch_cfg<RDYB_WARP_SHAPE_256, true>(q, nt, xq, euler, courant, stream);
+  return warp_launch_cfg<RDYB_WARP_SHAPE_256, false>(q, nt, xq, euler, courant, stream);
 }
 #endif

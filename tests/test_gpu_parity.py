@@ -15,14 +15,16 @@ from util import REL_TOL, assert_state_close, make_oracle, state_error
 
 pytestmark = pytest.mark.gpu
 
-KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP]
+WARP128 = (WARP, 128)  # K5 with 128-cell staged tiles and a 4-deep pipeline
+KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, WARP128]
 
 
 def _op(case, kernel=GATHER, **opts):
     op = Operator.from_case(case)
+    kernel, tile = kernel if isinstance(kernel, tuple) else (kernel, 256)
     if kernel != GATHER:
         try:
-            op.set_kernel(kernel, 256)
+            op.set_kernel(kernel, tile)
         except Exception as exc:
             if "not built" in str(exc):
                 pytest.skip("tiled kernel not built yet")
