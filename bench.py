@@ -40,11 +40,12 @@ def parse_args():
     p.add_argument("--nx", type=int, default=2236, help="quads per side of one GPU's block (cells = 2*nx*ny)")
     p.add_argument("--ny", type=int, default=0)
     p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed", "warp"])
-    p.add_argument("--tile", type=int, default=int(os.environ.get("RDYB_TILE", "256")))
+    p.add_argument("--tile", type=int, default=int(os.environ.get("RDYB_TILE", "224")))
     p.add_argument("--no-courant", action="store_true", help="skip the per-edge Courant diagnostic (the reference always computes it)")
     p.add_argument("--e2e-steps", type=int, default=10)
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--eta0", type=float, default=None, help="initial lake level (default 18 m: ~55 %% of the cells wet; experiments only)")
     p.add_argument("--hr", action="store_true", help="config D: hydrostatic reconstruction + dam column")
     return p.parse_args()
 
@@ -232,7 +233,7 @@ def run_b200_arm(args):
     if args.hr:
         case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=12.0, hr=True, px=px, py=py, rank=rank, dam_column=(2000.0, 28.0))
     else:
-        case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=18.0, px=px, py=py, rank=rank)
+        case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=18.0 if args.eta0 is None else args.eta0, px=px, py=py, rank=rank)
     halo = case.mesh.halo() if world > 1 else None
     op = Operator.from_case(case, device=local_rank, halo=halo)
     kernel = {"auto": TILED_FIXED, "gather": GATHER, "tiled": TILED, "async": TILED_ASYNC, "fixed": TILED_FIXED, "warp": WARP}[args.kernel]

@@ -44,6 +44,19 @@ __device__ __forceinline__ double swe_sqrt(double a) {
   return a > 0.0 ? s : 0.0;
 }
 
+/* a^(-1/3) for normal positive a (depths in [tiny_h, ~1e4]): fp32 MUFU seed exp2(-log2(a)/3) (~2^-21) + two Newton steps
+ * y <- y + y (1 - a y^3) / 3 (error e -> 2 e^2), ~15 instructions instead of the ~40 of the library rcbrt() with its
+ * exponent-splitting and special-case paths */
+__device__ __forceinline__ double swe_rcbrt(double a) {
+  double y = (double)exp2f(-0.333333343f * __log2f((float)a));
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const double e = fma(-(a * y), y * y, 1.0);
+    y = fma(y * e, 0.33333333333333331, y);
+  }
+  return y;
+}
+
 struct RoeFlux {
   double f0, f1, f2, amax;
 };
@@ -144,7 +157,7 @@ __device__ __forceinline__ void swe_friction(double h, double hu, double hv, dou
                                              double xq_thr, double &tbx, double &tby) {
   const double g = RDYB_GRAVITY;
   const double rh = swe_rcp(h);
-  const double rc = rcbrt(h); /* h^(-1/3) */
+  const double rc = swe_rcbrt(h); /* h^(-1/3) */
   if (METHOD == 0) {
     const double u = hu * rh, v = hv * rh;
     const double Cd = g * (n * n) * rc;

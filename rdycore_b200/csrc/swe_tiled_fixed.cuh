@@ -41,15 +41,17 @@ template <int TC, int HM, int ME, bool HR>
 struct alignas(16) FixedScratch {
   static constexpr int CS = TC + HM;
   double u[CS], v[CS], sq[HR ? 2 : CS];
-  double f0[ME], f1[ME], f2[ME];
-  double c1l[HR ? ME : 2], c2l[HR ? ME : 2], c1r[HR ? ME : 2], c2r[HR ? ME : 2];
+  /* the edge fluxes overwrite the edge geometry of the stage in place (esn <- f0, ecn <- f1, elen <- f2: an edge's thread reads
+   * its geometry before it writes its flux).  HR: f1, f2 hold momentum flux + pressure correction as seen by the LEFT cell,
+   * f1r, f2r as seen by the RIGHT cell */
+  double f1r[HR ? ME : 2], f2r[HR ? ME : 2];
 };
 
-template <int TC, int HM, int ME, bool HR>
+template <int TC, int HM, int ME, int NS, bool HR>
 struct FixedSmem {
-  FixedStage<TC, HM, ME, HR> st[2];
+  FixedStage<TC, HM, ME, HR> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
   FixedScratch<TC, HM, ME, HR> sc;
-  uint64_t full_bar[2], empty_bar[2];
+  uint64_t full_bar[NS], empty_bar[NS];
   double wval[16];
   int wargs[16];
 };
@@ -62,21 +64,22 @@ struct FixedArgs {
 template <int NCONS>
 __device__ __forceinline__ void fixed_consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory"); }
 
-template <int TC, int HM, int ME, int NCONS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
 __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const FixedArgs q) {
   extern __shared__ __align__(128) char smem_raw[];
-  using Smem = FixedSmem<TC, HM, ME, HR>;
+  using Smem = FixedSmem<TC, HM, ME, NS, HR>;
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const TiledArgs &p = q.t;
   const SweArgs &a = p.a;
   constexpr int HK = (HM + 31) / 32; /* halo indices per producer lane */
   if (threadIdx.x == 0) {
-    mbar_init(&S.full_bar[0], 33); mbar_init(&S.full_bar[1], 33);
-    mbar_init(&S.empty_bar[0], NCONS); mbar_init(&S.empty_bar[1], NCONS);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], NCONS);
+      /* the zero flux entry that empty cell-edge slots point at (never touched by the bulk copies: nedge <= ME - 2) */
+      S.st[s].esn[ME - 1] = 0.0; S.st[s].ecn[ME - 1] = 0.0; S.st[s].elen[ME - 1] = 0.0;
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    /* the zero flux entry that empty cell-edge slots point at */
-    S.sc.f0[ME - 1] = 0.0; S.sc.f1[ME - 1] = 0.0; S.sc.f2[ME - 1] = 0.0;
-    if (HR) { S.sc.c1l[ME - 1] = 0.0; S.sc.c2l[ME - 1] = 0.0; S.sc.c1r[ME - 1] = 0.0; S.sc.c2r[ME - 1] = 0.0; }
+    if (HR) { S.sc.f1r[ME - 1] = 0.0; S.sc.f2r[ME - 1] = 0.0; }
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -99,7 +102,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
 #pragma unroll
     for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; hidx[k] = t < d1.y ? __ldg(p.halo_cells + d1.x + t) : 0; }
     for (int it = 0; tile < q.tile_end; tile += G, ++it) {
-      const int s = it & 1;
+      const int s = it % NS;
       /* prefetch: descriptor two tiles ahead, halo index list one tile ahead */
       int4 nn0 = make_int4(0, 0, 0, 0);
       int2 nn1 = make_int2(0, 0);
@@ -110,7 +113,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       int nh[HK];
 #pragma unroll
       for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; nh[k] = t < n1.y ? __ldg(p.halo_cells + n1.x + t) : 0; }
-      mbar_wait(&S.empty_bar[s], ((it >> 1) & 1) ^ 1);
+      mbar_wait(&S.empty_bar[s], ((it / NS) & 1) ^ 1);
       auto &st = S.st[s];
       const int cb = d0.x, ncell = d0.y, eo = d0.z, nedge = d0.w, nhalo = d1.y;
       uint64_t *bar = &S.full_bar[s];
@@ -166,11 +169,16 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
   int carg = -1;
   int it = 0;
   for (int tile = q.tile_begin + blockIdx.x; tile < q.tile_end; tile += G, ++it) {
-    const int s = it & 1;
-    mbar_wait(&S.full_bar[s], (it >> 1) & 1);
+    const int s = it % NS;
+    mbar_wait(&S.full_bar[s], (it / NS) & 1);
     auto &st = S.st[s];
     const int cb = st.desc[0], ncell = st.desc[1], eo = st.desc[2], nedge = st.desc[3], nhalo = st.desc[5];
 
+    if (p.tile0 == 1) { /* experiment (RDYB_DEBUG_COPYONLY=1): the staging pipeline alone, no arithmetic */
+      for (int t = tid; t < ncell; t += NCONS) { a.o0[cb + t] = st.h[t]; a.o1[cb + t] = st.hu[t]; a.o2[cb + t] = st.hv[t]; }
+      mbar_arrive(&S.empty_bar[s]);
+      continue;
+    }
     /* ---- phase 1: primitive state of the staged cells: tile cells [0,TC) and halo cells [TC,TC+nhalo) ---- */
     for (int x = tid; x < TC + nhalo; x += NCONS) {
       const double h = st.h[x];
@@ -243,8 +251,9 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
           a.bacc[j] += dt * f.f0; a.bacc[a.nbe + j] += dt * f.f1; a.bacc[2 * a.nbe + j] += dt * f.f2;
         }
       }
-      sc.f0[e] = f.f0 * len; sc.f1[e] = f.f1 * len; sc.f2[e] = f.f2 * len;
-      if (HR) { sc.c1l[e] = k1l; sc.c2l[e] = k2l; sc.c1r[e] = k1r; sc.c2r[e] = k2r; }
+      const double fl1 = f.f1 * len, fl2 = f.f2 * len;
+      st.esn[e] = f.f0 * len; st.ecn[e] = fl1 + k1l; st.elen[e] = fl2 + k2l; /* in place of the edge geometry */
+      if (HR) { sc.f1r[e] = fl1 + k1r; sc.f2r[e] = fl2 + k2r; }
     }
     fixed_consumer_sync<NCONS>();
 
@@ -261,11 +270,13 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
           const int e = min((int)(ce & 0x7fffu), ME - 1);                  /* empty slot (0xffff) -> the zero flux entry */
           const int flip = (int)((~ce & 0x8000u) << 16);                   /* left cell: -1/area, right cell: +1/area */
           const double sgn = __hiloint2double(ia_hi ^ flip, ia_lo);
-          F0 = fma(sc.f0[e], sgn, F0); F1 = fma(sc.f1[e], sgn, F1); F2 = fma(sc.f2[e], sgn, F2);
+          F0 = fma(st.esn[e], sgn, F0);
           if (HR) {
             const bool right = (ce & 0x8000u) != 0;
-            F1 = fma(right ? sc.c1r[e] : sc.c1l[e], sgn, F1);
-            F2 = fma(right ? sc.c2r[e] : sc.c2l[e], sgn, F2);
+            F1 = fma(right ? sc.f1r[e] : st.ecn[e], sgn, F1);
+            F2 = fma(right ? sc.f2r[e] : st.elen[e], sgn, F2);
+          } else {
+            F1 = fma(st.ecn[e], sgn, F1); F2 = fma(st.elen[e], sgn, F2);
           }
         }
       }
@@ -308,12 +319,12 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
 }
 
 /* ---------------- host side ---------------- */
-template <int TC, int HM, int ME, int NCONS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
 static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
   static bool configured = false;
   static int blocks_per_sm = 0, num_sms = 0;
-  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, MINB, HR, SRC, EULER, COURANT>;
-  const size_t smem = sizeof(FixedSmem<TC, HM, ME, HR>);
+  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, NS, MINB, HR, SRC, EULER, COURANT>;
+  const size_t smem = sizeof(FixedSmem<TC, HM, ME, NS, HR>);
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "fixed tile kernel: %zu bytes of shared memory per CTA not available (%s)", smem, cudaGetErrorString(e));
@@ -333,31 +344,31 @@ static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
   return RDYB_SUCCESS;
 }
 
-template <int TC, int HM, int ME, int NCONS, int MINB, bool HR>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR>
 static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
 #define FL(SRCv)                                                                                                                   \
-  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, true, true>(q, nt, stream)                                  \
-                    : fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, true, false>(q, nt, stream))                                \
-         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, false, true>(q, nt, stream)                                 \
-                    : fixed_launch_t<TC, HM, ME, NCONS, MINB, HR, SRCv, false, false>(q, nt, stream)))
+  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, true>(q, nt, stream)                                  \
+                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, false>(q, nt, stream))                                \
+         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, true>(q, nt, stream)                                 \
+                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, false>(q, nt, stream)))
   return xq ? FL(1) : FL(0);
 #undef FL
 }
 
-/* the compiled tile shapes: {tile cells, halo capacity, edge capacity (one entry is the zero flux), consumer threads, CTAs/SM} */
-#define RDYB_FIXED_A 256, 96, 576, 256, 2 /* triangles, quads and mixed meshes */
-#define RDYB_FIXED_B 320, 96, 544, 256, 2 /* triangle meshes: ~1.6 edges per cell fill two full passes of 256 threads */
-#define RDYB_FIXED_C 256, 96, 448, 256, 2 /* hydrostatic reconstruction on triangle meshes */
+/* the compiled tile shapes: {tile cells, halo capacity, edge capacity (the last entry is the zero flux), consumer threads,
+ * pipeline stages, CTAs/SM} */
+#define RDYB_FIXED_A 256, 96, 576, 256, 2, 2 /* quads and mixed meshes (2 edges per cell) */
+#define RDYB_FIXED_T 256, 80, 448, 256, 3, 2 /* triangle meshes (1.6 edges per cell): room for a third stage */
+#define RDYB_FIXED_S 224, 80, 400, 224, 2, 3 /* triangle meshes, 7 consumer warps: three CTAs (21 consumer warps) per SM */
+static inline bool fixed_fits_s(const RdybTiledLayout &T) { return T.tile_cells == 224 && T.max_halo <= 80 && T.max_edges <= 398; }
 
+static inline bool fixed_fits_t(const RdybTiledLayout &T) { return T.tile_cells == 256 && T.max_halo <= 80 && T.max_edges <= 446; }
+static inline bool fixed_fits_a(const RdybTiledLayout &T) { return T.tile_cells == 256 && T.max_halo <= 96 && T.max_edges <= 574; }
 /* true when K4 has a compiled shape for this layout and option set */
 static inline bool tiled_fixed_applicable(const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a) {
+  (void)cfg;
   if (a.s1 || a.s2) return false; /* momentum sources: K3 */
-  if (T.max_halo > 96) return false;
-  const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
-  if (hr) return T.tile_cells == 256 && T.max_edges <= 447;
-  if (T.tile_cells == 256) return T.max_edges <= 575;
-  if (T.tile_cells == 320) return T.max_edges <= 543;
-  return false;
+  return fixed_fits_t(T) || fixed_fits_a(T) || fixed_fits_s(T);
 }
 
 static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a, int32_t n_interior,
@@ -369,14 +380,17 @@ static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T
   p.edge_offsets = d.edge_offsets; p.edge_bidx = d.edge_bidx; p.edge_lr = d.edge_lr; p.edge_sn = d.edge_sn; p.edge_cn = d.edge_cn;
   p.edge_len = d.edge_len; p.cell_edges = d.cell_edges;
   p.tile0 = 0; p.max_cells = T.tile_cells; p.max_staged = 0; p.max_edges = 0;
+  { const char *dbg = getenv("RDYB_DEBUG_COPYONLY"); if (dbg && dbg[0] == '1') p.tile0 = 1; }
   q.tile_begin = a.begin < n_interior ? 0 : T.num_interior_tiles;
   q.tile_end = (a.end <= n_interior && a.begin < n_interior) ? T.num_interior_tiles : T.num_tiles;
   if (q.tile_end <= q.tile_begin) return RDYB_SUCCESS;
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
   const int nt = q.tile_end - q.tile_begin;
-  if (hr) return fixed_launch_cfg<RDYB_FIXED_C, true>(q, nt, xq, euler, courant, stream);
-  if (T.tile_cells == 320) return fixed_launch_cfg<RDYB_FIXED_B, false>(q, nt, xq, euler, courant, stream);
-  return fixed_launch_cfg<RDYB_FIXED_A, false>(q, nt, xq, euler, courant, stream);
+  const char *env = getenv("RDYB_FIXED_SHAPE"); /* experiments: "A" forces the 2-stage shape */
+  if (fixed_fits_s(T)) return hr ? fixed_launch_cfg<RDYB_FIXED_S, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_S, false>(q, nt, xq, euler, courant, stream);
+  const bool use_t = fixed_fits_t(T) && !(env && env[0] == 'A');
+  if (use_t) return hr ? fixed_launch_cfg<RDYB_FIXED_T, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_T, false>(q, nt, xq, euler, courant, stream);
+  return hr ? fixed_launch_cfg<RDYB_FIXED_A, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_A, false>(q, nt, xq, euler, courant, stream);
 }
 #endif

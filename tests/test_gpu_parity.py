@@ -16,7 +16,8 @@ from util import REL_TOL, assert_state_close, make_oracle, state_error
 pytestmark = pytest.mark.gpu
 
 WARP128 = (WARP, 128)  # K5 with 128-cell staged tiles and a 4-deep pipeline
-KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, WARP128]
+FIXED224 = (TILED_FIXED, 224)  # K4 shape with 7 consumer warps and three CTAs per SM (the bench default)
+KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, FIXED224, WARP, WARP128]
 
 
 def _op(case, kernel=GATHER, **opts):
