@@ -189,6 +189,14 @@ int rdyb_nccl_unique_id(void *id128 /* 128 bytes out */);
 int rdyb_operator_init_comm(RdybOperator op, int32_t nranks, int32_t rank, const void *id128);
 /* run one halo exchange now (owned -> peers' ghosts) on the current state */
 int rdyb_operator_halo_exchange(RdybOperator op);
+/* Peer-memory halo for the fused Euler step (one process per GPU on one NVLink box): every rank exports a blob of
+ * RDYB_HALO_BLOB_BYTES (CUDA IPC handles of its state buffers and flag words + its halo plan), the host gathers the blobs of
+ * all ranks by any means (MPI_Allgather on the RDycore side) and hands the nranks*RDYB_HALO_BLOB_BYTES array to import.
+ * Afterwards rdyb_operator_step_euler writes border cells straight into the neighbours' ghost slots over NVLink instead of
+ * going through pack -> ncclSend/ncclRecv -> unpack.  Collective: all ranks must call step_euler with the same step counts. */
+#define RDYB_HALO_BLOB_BYTES 512
+int rdyb_operator_halo_export(RdybOperator op, int32_t rank, void *blob);
+int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_t rank, const void *blobs);
 
 /* ---- raw device pointers (for zero-copy binding to VECCUDA / torch tensors) ---- */
 /* which: 0..2 = h,hu,hv current state (length num_local), 3..5 = F (length num_owned) */
@@ -196,6 +204,9 @@ int rdyb_operator_device_pointer(RdybOperator op, int32_t which, void **ptr, int
 /* timing helper: average kernel time of the last step_euler call's main kernel, measured with
  * CUDA events on the operator's stream (ms per launch) */
 int rdyb_operator_last_kernel_ms(RdybOperator op, double *ms_per_launch, int32_t *launches);
+/* text description of the kernel the last launch ran and of the device layout (a requested kernel falls back to a more
+ * general one when the mesh does not fit its compiled tile shapes) */
+int rdyb_operator_kernel_info(RdybOperator op, char *buf, int32_t len);
 
 #ifdef __cplusplus
 }

@@ -376,6 +376,8 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
     nh += nth; ne += nte;
     if (nth > T->max_halo) T->max_halo = nth;
     if (nte > T->max_edges) T->max_edges = nte;
+    if (t < nt_int && nth > T->max_halo_interior) T->max_halo_interior = nth;
+    if (t < nt_int && nte > T->max_edges_interior) T->max_edges_interior = nte;
     if (ne > INT32_MAX - 65536 || nh > INT32_MAX - 65536) { ierr = rdyb_fail(RDYB_ERR_SUP, "tiled layout: too many tile edges for int32 offsets"); goto fail; }
   }
   T->tile_cell_begin[nt] = N; T->halo_offsets[nt] = (int32_t)nh; T->edge_offsets[nt] = (int32_t)ne;

@@ -62,6 +62,7 @@ typedef struct {
   int32_t num_tiles;
   int32_t num_interior_tiles; /* tiles [0,num_interior_tiles) cover interior cells only */
   int32_t max_halo, max_edges; /* per-tile maxima (shared-memory sizing) */
+  int32_t max_halo_interior, max_edges_interior; /* the same over the interior tiles only (frontier tiles are thin strips with many more outside neighbours) */
   int32_t *tile_cell_begin;  /* [num_tiles+1] device cell ranges */
   int32_t *tile_desc;        /* [8*num_tiles] per tile {cell_begin, ncell, edge_begin, nedge, halo_begin, nhalo, 0, 0}; begins are padded to 4 */
   int32_t *halo_offsets;     /* [num_tiles+1] into halo_cells */

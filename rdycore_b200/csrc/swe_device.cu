@@ -108,12 +108,20 @@ struct RdybOperator_ {
   /* warp-tile kernel (K5) */
   RdybWarpLayout WL;
   WarpDev wd;
+  const char *last_kernel = "none";
   bool has_warp = false, warp_used = false; /* warp_used: the last launch ran K5 (not a fallback) */
   int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3),
                           4 = one 32-cell mini-tile per warp (K5; falls back to K4 / K3) */
   /* options */
   bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
   bool mom_src = false; /* any momentum external source set */
+  /* peer-memory halo (Euler fast path) */
+  bool p2p = false;
+  PeerTable ptab;
+  unsigned int p2p_epoch = 0;
+  unsigned int *p2p_flags = nullptr; /* [RDYB_MAX_PEERS] counters raised by the neighbours, + 1 status word */
+  void *p2p_opened[3 * RDYB_MAX_PEERS];
+  int p2p_nopened = 0;
   /* comm */
   ncclComm_t comm = nullptr;
   int32_t nranks = 1, rank = 0;
@@ -145,6 +153,8 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   cudaSetDevice(op->device);
   if (op->stream) cudaStreamSynchronize(op->stream);
   if (op->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(op->comm);
+  for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]);
+  if (op->p2p_flags) cudaFree(op->p2p_flags);
   void *ptrs[] = {op->state[0], op->state[1], op->F, op->src, op->mann, op->fdiv, op->prim, op->inv_area, op->area, op->dzdx, op->dzdy, op->zc,
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
                   op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
@@ -234,6 +244,7 @@ extern "C" int rdyb_operator_create(const RdybConfig *config, const RdybMeshView
   memset(&op->td, 0, sizeof(op->td));
   memset(&op->WL, 0, sizeof(op->WL));
   memset(&op->wd, 0, sizeof(op->wd));
+  memset(&op->ptab, 0, sizeof(op->ptab));
   int ierr = operator_create_impl(op, config, mesh, nb, bnd, halo, device, cuda_stream);
   if (ierr) {
     char saved[1024];
@@ -476,15 +487,30 @@ static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
 static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
   if (end <= begin) return RDYB_SUCCESS;
   if (op->kernel_kind >= 1 && op->has_tiled) {
+    /* interior tiles and frontier tiles (thin strips along the partition border, with many more outside neighbours) are
+     * launched separately so that each part can use the most specialised kernel its tiles fit */
+    if (begin < op->NI && end > op->NI) {
+      RDYB_CALL(launch_cells(op, in, out, dt, euler, begin, op->NI, cslot0));
+      return launch_cells(op, in, out, dt, euler, op->NI, end, cslot0);
+    }
     SweArgs t;
     fill_args(op, t, in, out, dt);
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile, indexed by tile number */
+    const bool interior = end <= op->NI;
+    const int mh = interior ? op->T.max_halo_interior : op->T.max_halo, me = interior ? op->T.max_edges_interior : op->T.max_edges;
     op->warp_used = op->kernel_kind == 4 && op->has_warp && warp_applicable(op->WL, t);
-    if (op->warp_used) RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
-    else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T, op->cfg, t)) RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
-    else if (op->kernel_kind >= 2) RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
-    else RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    if (op->warp_used) { op->last_kernel = "swe_warp_kernel (K5)"; RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream)); }
+    else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T.tile_cells, mh, me, t)) {
+      if (interior || op->NI == 0) op->last_kernel = "swe_tiled_fixed_kernel (K4)";
+      RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, mh, me, op->stream));
+    } else if (op->kernel_kind >= 2) {
+      if (interior || op->NI == 0) op->last_kernel = "swe_tiled_async_kernel (K3)";
+      RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    } else {
+      op->last_kernel = "swe_tiled_kernel (K2)";
+      RDYB_CALL(tiled_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    }
     LAUNCHED();
     CU(cudaGetLastError());
     return RDYB_SUCCESS;
@@ -493,6 +519,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
   fill_args(op, a, in, out, dt);
   a.begin = begin; a.end = end;
   if (op->opt_courant) { a.cmax = op->cmax + cslot0; a.carg = op->carg + cslot0; }
+  op->last_kernel = "swe_gather_kernel (K1)";
   const int grid = grid_for(end - begin, RDYB_BLOCK);
   if (euler) launch_gather<true>(op, a, grid);
   else launch_gather<false>(op, a, grid);
@@ -565,6 +592,88 @@ extern "C" int rdyb_operator_halo_exchange(RdybOperator op) {
   return RDYB_SUCCESS;
 }
 
+
+/* ---------------- peer-memory halo: export / import of the CUDA IPC handles ---------------- */
+struct HaloBlob { /* <= RDYB_HALO_BLOB_BYTES */
+  uint32_t magic;
+  int32_t rank, n_owned, stride, num_peers;
+  int32_t peer_ranks[RDYB_MAX_PEERS];
+  int32_t recv_offsets[RDYB_MAX_PEERS + 1];
+  int32_t send_counts[RDYB_MAX_PEERS];
+  cudaIpcMemHandle_t state[2], flags;
+};
+static_assert(sizeof(HaloBlob) <= RDYB_HALO_BLOB_BYTES, "halo blob does not fit its public size");
+
+extern "C" int rdyb_operator_halo_export(RdybOperator op, int32_t rank, void *blob) {
+  RDYB_CHECK(op && blob, RDYB_ERR_ARG, "NULL argument");
+  const RdybLayout &L = op->L;
+  RDYB_CHECK(L.num_peers <= RDYB_MAX_PEERS, RDYB_ERR_SUP, "peer-memory halo supports at most %d neighbours per rank (this rank has %d)", RDYB_MAX_PEERS, L.num_peers);
+  CU(cudaSetDevice(op->device));
+  if (!op->p2p_flags) RDYB_CALL(dalloc(&op->p2p_flags, RDYB_MAX_PEERS + 8));
+  HaloBlob b;
+  memset(&b, 0, sizeof(b));
+  b.magic = 0x52445942u; b.rank = rank; b.n_owned = op->N; b.stride = op->stride; b.num_peers = L.num_peers;
+  for (int p = 0; p < L.num_peers; ++p) { b.peer_ranks[p] = L.peer_ranks[p]; b.recv_offsets[p] = L.recv_offsets[p]; b.send_counts[p] = L.send_offsets[p + 1] - L.send_offsets[p]; }
+  if (L.num_peers > 0) b.recv_offsets[L.num_peers] = L.recv_offsets[L.num_peers];
+  CU(cudaIpcGetMemHandle(&b.state[0], op->state[0]));
+  CU(cudaIpcGetMemHandle(&b.state[1], op->state[1]));
+  CU(cudaIpcGetMemHandle(&b.flags, op->p2p_flags));
+  memset(blob, 0, RDYB_HALO_BLOB_BYTES);
+  memcpy(blob, &b, sizeof(b));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_t rank, const void *blobs) {
+  RDYB_CHECK(op && blobs, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(op->p2p_flags, RDYB_ERR_USER, "rdyb_operator_halo_export must be called before rdyb_operator_halo_import");
+  const RdybLayout &L = op->L;
+  CU(cudaSetDevice(op->device));
+  PeerTable &t = op->ptab;
+  memset(&t, 0, sizeof(t));
+  t.num_peers = L.num_peers;
+  for (int p = 0; p < L.num_peers; ++p) {
+    const int r = L.peer_ranks[p];
+    RDYB_CHECK(r >= 0 && r < nranks && r != rank, RDYB_ERR_USER, "halo plan names rank %d (of %d) as a neighbour of rank %d", r, nranks, rank);
+    HaloBlob b;
+    memcpy(&b, (const char *)blobs + (size_t)r * RDYB_HALO_BLOB_BYTES, sizeof(b));
+    RDYB_CHECK(b.magic == 0x52445942u && b.rank == r, RDYB_ERR_USER, "halo blob of rank %d is missing or corrupt", r);
+    int q = -1;
+    for (int j = 0; j < b.num_peers; ++j) if (b.peer_ranks[j] == rank) q = j;
+    RDYB_CHECK(q >= 0, RDYB_ERR_USER, "rank %d sends to rank %d, which does not list it as a neighbour", rank, r);
+    const int nsend = L.send_offsets[p + 1] - L.send_offsets[p], nrecv_there = b.recv_offsets[q + 1] - b.recv_offsets[q];
+    RDYB_CHECK(nsend == nrecv_there, RDYB_ERR_USER, "rank %d sends %d cells to rank %d, which expects %d", rank, nsend, r, nrecv_there);
+    void *ptr[3];
+    const cudaIpcMemHandle_t hs[3] = {b.state[0], b.state[1], b.flags};
+    for (int k = 0; k < 3; ++k) {
+      CU(cudaIpcOpenMemHandle(&ptr[k], hs[k], cudaIpcMemLazyEnablePeerAccess));
+      op->p2p_opened[op->p2p_nopened++] = ptr[k];
+    }
+    t.state[p][0] = (double *)ptr[0]; t.state[p][1] = (double *)ptr[1];
+    t.flag[p] = (unsigned int *)ptr[2] + q;
+    t.stride[p] = b.stride; t.ghost0[p] = b.n_owned + b.recv_offsets[q];
+    t.send_begin[p] = L.send_offsets[p];
+  }
+  t.send_begin[L.num_peers] = L.num_peers ? L.send_offsets[L.num_peers] : 0;
+  op->p2p = L.num_peers > 0;
+  op->p2p_epoch = 0;
+  return RDYB_SUCCESS;
+}
+
+/* push the border cells of `state` (buffer index buf) into the neighbours' ghost slots and raise the step counter */
+static int p2p_push(RdybOperator op, const double *state, int buf) {
+  halo_push_kernel<<<1, 1024, 0, op->stream>>>(state, op->stride, op->send_cells, op->ptab, buf, ++op->p2p_epoch);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  return RDYB_SUCCESS;
+}
+static int p2p_wait(RdybOperator op) {
+  halo_wait_kernel<<<1, 32, 0, op->stream>>>(op->p2p_flags, op->ptab.num_peers, op->p2p_epoch, 6000000000ll /* ~3 s */,
+                                            reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS));
+  LAUNCHED();
+  CU(cudaGetLastError());
+  return RDYB_SUCCESS;
+}
+
 /* one RHS (or fused Euler) evaluation of `in` into `out`, with the halo exchange of `in` overlapped with the interior cells */
 static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool euler) {
   const bool exchange = op->L.num_peers > 0 && op->comm;
@@ -620,9 +729,23 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
   RDYB_CHECK(nsteps >= 0, RDYB_ERR_ARG, "negative step count");
   CU(cudaSetDevice(op->device));
   CU(cudaEventRecord(op->ev_t0, op->stream));
-  for (int32_t s = 0; s < nsteps; ++s) {
-    RDYB_CALL(rhs_pass(op, op->state[op->cur], op->state[op->cur ^ 1], dt, true));
-    op->cur ^= 1;
+  if (op->p2p && nsteps > 0) {
+    /* peer-memory halo: the two state buffers alternate, so a neighbour's push for step s+1 lands in the buffer this rank
+     * does not read during step s, and its counter (raised after its frontier kernel) orders everything else */
+    RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+    for (int32_t s = 0; s < nsteps; ++s) {
+      double *in = op->state[op->cur], *out = op->state[op->cur ^ 1];
+      RDYB_CALL(launch_cells(op, in, out, dt, true, 0, op->NI, 0));                       /* interior cells: no ghost needed */
+      RDYB_CALL(p2p_wait(op));                                                          /* neighbours' border cells have landed */
+      RDYB_CALL(launch_cells(op, in, out, dt, true, op->NI, op->N, op->ncblocks_interior)); /* frontier cells */
+      op->cur ^= 1;
+      if (s + 1 < nsteps) RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+    }
+  } else {
+    for (int32_t s = 0; s < nsteps; ++s) {
+      RDYB_CALL(rhs_pass(op, op->state[op->cur], op->state[op->cur ^ 1], dt, true));
+      op->cur ^= 1;
+    }
   }
   CU(cudaEventRecord(op->ev_t1, op->stream));
   op->last_launches = nsteps;
@@ -665,6 +788,14 @@ extern "C" int rdyb_operator_synchronize(RdybOperator op) {
   CU(cudaSetDevice(op->device));
   CU(cudaStreamSynchronize(op->comm_stream));
   CU(cudaStreamSynchronize(op->stream));
+  if (op->p2p) {
+    int status = 0;
+    CU(cudaMemcpy(&status, op->p2p_flags + RDYB_MAX_PEERS, sizeof(int), cudaMemcpyDeviceToHost));
+    if (status) {
+      CU(cudaMemset(op->p2p_flags + RDYB_MAX_PEERS, 0, sizeof(int)));
+      return rdyb_fail(RDYB_ERR_NCCL, "peer-memory halo: neighbour %d (rank %d) did not deliver its border cells in time", status - 1, op->L.peer_ranks[status - 1]);
+    }
+  }
   return RDYB_SUCCESS;
 }
 
@@ -738,6 +869,16 @@ extern "C" int rdyb_operator_last_kernel_ms(RdybOperator op, double *ms_per_laun
   CU(cudaEventElapsedTime(&ms, op->ev_t0, op->ev_t1));
   *ms_per_launch = op->last_launches > 0 ? (double)ms / op->last_launches : 0.0;
   if (launches) *launches = op->last_launches;
+  return RDYB_SUCCESS;
+}
+
+/* which kernel the last RHS / step launch ran (a requested kernel falls back when a mesh does not fit its compiled shapes) */
+extern "C" int rdyb_operator_kernel_info(RdybOperator op, char *buf, int32_t len) {
+  RDYB_CHECK(op && buf && len > 0, RDYB_ERR_ARG, "NULL argument");
+  if (op->kernel_kind >= 1 && op->has_tiled)
+    snprintf(buf, (size_t)len, "%s; tiles %d x %d cells, max halo %d, max edges %d; interior cells %d of %d owned, %d local", op->last_kernel, op->T.num_tiles,
+             op->T.tile_cells, op->T.max_halo, op->T.max_edges, op->NI, op->N, op->NL);
+  else snprintf(buf, (size_t)len, "%s; interior cells %d of %d owned, %d local", op->last_kernel, op->NI, op->N, op->NL);
   return RDYB_SUCCESS;
 }
 

@@ -231,6 +231,50 @@ __global__ void halo_unpack_kernel(const double *__restrict__ buf, double *__res
   }
 }
 
+/* ---- peer-memory halo (NVLink P2P): the owner writes its border cells straight into the neighbours' ghost slots ----
+ * Replaces DMGlobalToLocalBegin/End (src/rdysetup.c:1133-1134) on the Euler fast path: no pack buffer, no NCCL kernel, no
+ * unpack; one small kernel per step stores 24 B per shared-face cell over NVLink and then raises a step counter in each
+ * neighbour's flag word; the neighbour's stream waits for that counter before its frontier cells run. */
+#define RDYB_MAX_PEERS 8
+struct PeerTable {
+  double *state[RDYB_MAX_PEERS][2];   /* neighbour's two state buffers (ping-pong), mapped through CUDA IPC */
+  unsigned int *flag[RDYB_MAX_PEERS]; /* the word in the neighbour's flag array that belongs to this rank */
+  int32_t stride[RDYB_MAX_PEERS];     /* neighbour's leading dimension */
+  int32_t ghost0[RDYB_MAX_PEERS];     /* neighbour's device index of the first ghost cell it receives from this rank */
+  int32_t send_begin[RDYB_MAX_PEERS + 1];
+  int32_t num_peers;
+};
+__global__ void __launch_bounds__(1024) halo_push_kernel(const double *__restrict__ state, int32_t stride, const int32_t *__restrict__ send_cells,
+                                                         const PeerTable tbl, int32_t buf, unsigned int epoch) {
+  for (int p = 0; p < tbl.num_peers; ++p) {
+    double *dst = tbl.state[p][buf];
+    const int32_t rs = tbl.stride[p], g0 = tbl.ghost0[p], b = tbl.send_begin[p], n = tbl.send_begin[p + 1] - b;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+      const int c = send_cells[b + k];
+      dst[g0 + k] = state[c]; dst[(size_t)rs + g0 + k] = state[(size_t)stride + c]; dst[2 * (size_t)rs + g0 + k] = state[2 * (size_t)stride + c];
+    }
+  }
+  __threadfence_system(); /* the stores above are visible system-wide before the counter */
+  __syncthreads();
+  if (threadIdx.x < tbl.num_peers) {
+    *reinterpret_cast<volatile unsigned int *>(tbl.flag[threadIdx.x]) = epoch;
+    __threadfence_system();
+  }
+}
+/* wait until every neighbour has raised its counter in my flag array to `epoch`; gives up after ~timeout_cycles and
+ * records the failure in *status (a hung peer must not hang this GPU) */
+__global__ void halo_wait_kernel(const unsigned int *flags, int32_t num_peers, unsigned int epoch, long long timeout_cycles, int *status) {
+  if (threadIdx.x < num_peers) {
+    const volatile unsigned int *f = flags + threadIdx.x;
+    const long long t0 = clock64();
+    while ((int)(*f - epoch) < 0) {
+      __nanosleep(100);
+      if (clock64() - t0 > timeout_cycles) { atomicExch(status, 1 + threadIdx.x); break; }
+    }
+  }
+  __threadfence_system();
+}
+
 /* y[c*stride+i] = x[c*stride+i] + w*k[c*stride+i], i < n (TSRK4 stage vectors) */
 __global__ void stage_axpy_kernel(const double *__restrict__ x, const double *__restrict__ k, double w, double *__restrict__ y, int32_t n, int32_t stride) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -360,19 +360,18 @@ static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, boo
 #define RDYB_FIXED_A 256, 96, 576, 256, 2, 2 /* quads and mixed meshes (2 edges per cell) */
 #define RDYB_FIXED_T 256, 80, 448, 256, 3, 2 /* triangle meshes (1.6 edges per cell): room for a third stage */
 #define RDYB_FIXED_S 224, 80, 400, 224, 2, 3 /* triangle meshes, 7 consumer warps: three CTAs (21 consumer warps) per SM */
-static inline bool fixed_fits_s(const RdybTiledLayout &T) { return T.tile_cells == 224 && T.max_halo <= 80 && T.max_edges <= 398; }
 
-static inline bool fixed_fits_t(const RdybTiledLayout &T) { return T.tile_cells == 256 && T.max_halo <= 80 && T.max_edges <= 446; }
-static inline bool fixed_fits_a(const RdybTiledLayout &T) { return T.tile_cells == 256 && T.max_halo <= 96 && T.max_edges <= 574; }
-/* true when K4 has a compiled shape for this layout and option set */
-static inline bool tiled_fixed_applicable(const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a) {
-  (void)cfg;
+static inline bool fixed_fits_t(int tc, int mh, int me) { return tc == 256 && mh <= 80 && me <= 446; }
+static inline bool fixed_fits_a(int tc, int mh, int me) { return tc == 256 && mh <= 96 && me <= 574; }
+static inline bool fixed_fits_s(int tc, int mh, int me) { return tc == 224 && mh <= 80 && me <= 398; }
+/* true when K4 has a compiled shape for tiles of tc cells with at most mh halo cells and me edges, and for this option set */
+static inline bool tiled_fixed_applicable(int tc, int mh, int me, const SweArgs &a) {
   if (a.s1 || a.s2) return false; /* momentum sources: K3 */
-  return fixed_fits_t(T) || fixed_fits_a(T) || fixed_fits_s(T);
+  return fixed_fits_t(tc, mh, me) || fixed_fits_a(tc, mh, me) || fixed_fits_s(tc, mh, me);
 }
 
 static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a, int32_t n_interior,
-                                     bool euler, bool courant, cudaStream_t stream) {
+                                     bool euler, bool courant, int max_halo, int max_edges, cudaStream_t stream) {
   FixedArgs q;
   TiledArgs &p = q.t;
   p.a = a;
@@ -388,8 +387,8 @@ static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
   const int nt = q.tile_end - q.tile_begin;
   const char *env = getenv("RDYB_FIXED_SHAPE"); /* experiments: "A" forces the 2-stage shape */
-  if (fixed_fits_s(T)) return hr ? fixed_launch_cfg<RDYB_FIXED_S, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_S, false>(q, nt, xq, euler, courant, stream);
-  const bool use_t = fixed_fits_t(T) && !(env && env[0] == 'A');
+  if (fixed_fits_s(T.tile_cells, max_halo, max_edges)) return hr ? fixed_launch_cfg<RDYB_FIXED_S, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_S, false>(q, nt, xq, euler, courant, stream);
+  const bool use_t = fixed_fits_t(T.tile_cells, max_halo, max_edges) && !(env && env[0] == 'A');
   if (use_t) return hr ? fixed_launch_cfg<RDYB_FIXED_T, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_T, false>(q, nt, xq, euler, courant, stream);
   return hr ? fixed_launch_cfg<RDYB_FIXED_A, true>(q, nt, xq, euler, courant, stream) : fixed_launch_cfg<RDYB_FIXED_A, false>(q, nt, xq, euler, courant, stream);
 }

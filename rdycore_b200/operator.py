@@ -152,6 +152,11 @@ class Operator:
         return ms.value, n.value
 
     # ---- diagnostics ----
+    def kernel_info(self) -> str:
+        buf = C.create_string_buffer(512)
+        check(lib().rdyb_operator_kernel_info(self._h, buf, C.c_int32(512)))
+        return buf.value.decode()
+
     def reset_diagnostics(self):
         check(lib().rdyb_operator_reset_diagnostics(self._h))
 
@@ -174,6 +179,19 @@ class Operator:
 
     def init_comm(self, nranks: int, rank: int, unique_id: bytes):
         check(lib().rdyb_operator_init_comm(self._h, C.c_int32(nranks), C.c_int32(rank), C.c_char_p(unique_id)))
+
+    HALO_BLOB_BYTES = 512
+
+    def halo_export(self, rank: int) -> bytes:
+        buf = C.create_string_buffer(self.HALO_BLOB_BYTES)
+        check(lib().rdyb_operator_halo_export(self._h, C.c_int32(rank), buf))
+        return buf.raw
+
+    def halo_import(self, nranks: int, rank: int, blobs: list) -> None:
+        """blobs: the halo_export() result of every rank, in rank order (gathered by the caller, e.g. all_gather_object)."""
+        raw = b"".join(blobs)
+        assert len(raw) == nranks * self.HALO_BLOB_BYTES
+        check(lib().rdyb_operator_halo_import(self._h, C.c_int32(nranks), C.c_int32(rank), raw))
 
     def halo_exchange(self):
         check(lib().rdyb_operator_halo_exchange(self._h))

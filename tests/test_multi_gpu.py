@@ -1,0 +1,46 @@
+"""GPU: the N > 1 path (partitioned mesh, per-step NCCL halo exchange overlapped with interior cells) against the serial CPU
+oracle.  Needs >= 2 GPUs; the worker is tests/multigpu_parity.py under torchrun (one process per GPU)."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpus():
+    try:
+        import torch
+
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _run(nranks, extra, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nranks}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "multigpu_parity.py"), *extra]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert p.returncode == 0 and "MULTIGPU_PARITY ok" in p.stdout, p.stdout[-3000:] + p.stderr[-3000:]
+    return p.stdout
+
+
+@pytest.mark.parametrize("kernel,tile", [(0, 0), (3, 224), (4, 256)])
+def test_two_ranks_nccl_halo_matches_serial_oracle(kernel, tile):
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, ["--kernel", str(kernel), "--tile", str(tile)], 29517 + kernel)
+
+
+def test_two_ranks_hydrostatic_reconstruction():
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, ["--hr", "--kernel", "3", "--tile", "224"], 29531)
+
+
+def test_four_ranks_2x2_blocks():
+    if _ngpus() < 4:
+        pytest.skip("needs 4 GPUs")
+    _run(4, ["--kernel", "3", "--tile", "224", "--nx", "128", "--ny", "96"], 29541)
