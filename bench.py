@@ -45,6 +45,7 @@ def parse_args():
     p.add_argument("--e2e-steps", type=int, default=10)
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--halo", default="p2p", choices=["p2p", "nccl"], help="N>1: peer-memory push over NVLink (CUDA IPC) or NCCL send/recv")
     p.add_argument("--eta0", type=float, default=None, help="initial lake level (default 18 m: ~55 %% of the cells wet; experiments only)")
     p.add_argument("--hr", action="store_true", help="config D: hydrostatic reconstruction + dam column")
     return p.parse_args()
@@ -244,6 +245,10 @@ def run_b200_arm(args):
         uid = [Operator.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         op.init_comm(world, rank, uid[0])
+        if args.halo == "p2p":
+            blobs = [None] * world
+            dist.all_gather_object(blobs, op.halo_export(rank))
+            op.halo_import(world, rank, blobs)
     t_setup = time.perf_counter() - t_setup
     n_owned = op.num_owned
 
@@ -275,6 +280,7 @@ def run_b200_arm(args):
     n0 = kernel_launch_count()
     op.step_euler(case.dt, args.steps)
     ms_per_step, _ = op.last_kernel_ms()  # event-synchronises
+    kinfo = op.kernel_info()
     barrier()
     launches = kernel_launch_count() - n0
     clocks = sampler.stop()
@@ -323,7 +329,8 @@ def run_b200_arm(args):
                 "workload": ("config D: HR floodplain" if args.hr else "config C: synthetic unstructured triangle floodplain")
                 + f", {args.nx}x{ny}x2 = {2 * args.nx * ny} cells per GPU, bathymetry + Manning n + rain, reflecting walls, "
                 + ("XQ2018" if False else "semi-implicit") + " friction, forward Euler",
-                "cells_total": int(total_cells), "decomposition": f"{px}x{py} blocks, 1 ghost layer, NCCL send/recv halo per step" if world > 1 else "single GPU",
+                "cells_total": int(total_cells), "decomposition": (f"{px}x{py} blocks, 1 ghost layer, per-step halo: " + ("border cells pushed into the neighbours' ghost slots over NVLink (CUDA IPC peer memory)" if args.halo == "p2p" else "NCCL send/recv")) if world > 1 else "single GPU",
+                "kernel_info": kinfo,
                 "kernel": kernel_name, "tile_cells": args.tile if kernel != GATHER else None, "courant_diagnostic": not args.no_courant,
                 "l2": "inputs larger than L2 (state 240 MB + mesh > 1 GB per GPU vs 126 MB L2); no flush needed",
                 "dt": case.dt, "setup_s": round(t_setup, 2),

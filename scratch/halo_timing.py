@@ -30,6 +30,12 @@ def halo(n):
     for _ in range(n): op.halo_exchange()
 halo(5)
 t_halo = timeit(halo, 200)
+blobs = [None] * world
+dist.all_gather_object(blobs, op.halo_export(rank))
+op.halo_import(world, rank, blobs)
+op.step_euler(case.dt, 5)
+t_p2p = timeit(lambda n: op.step_euler(case.dt, n), 200)
 if rank == 0:
+    print(f"HALO_TIMING p2p full step {t_p2p:.4f} ms", flush=True)
     print(f"HALO_TIMING ranks={world} owned={op.num_owned} local={op.num_local} ms/step: no-comm {t_nocomm:.4f}  full {t_full:.4f}  halo-exchange alone {t_halo:.4f}", flush=True)
 op.close(); dist.barrier(); dist.destroy_process_group()

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--ny", type=int, default=64)
     ap.add_argument("--kernel", type=int, default=3)
     ap.add_argument("--tile", type=int, default=224)
+    ap.add_argument("--p2p", action="store_true", help="peer-memory halo (CUDA IPC over NVLink) instead of NCCL send/recv")
     args = ap.parse_args()
 
     import torch
@@ -52,6 +53,10 @@ def main():
     uid = [Operator.nccl_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     op.init_comm(world, rank, uid[0])
+    if args.p2p:
+        blobs = [None] * world
+        dist.all_gather_object(blobs, op.halo_export(rank))
+        op.halo_import(world, rank, blobs)
     m0 = torch.tensor([op.mass()], dtype=torch.float64, device="cuda")
     op.step_euler(serial.dt, args.steps - 1)
     op.reset_diagnostics()  # the oracle's Courant diagnostic covers its last RHS evaluation only
@@ -90,7 +95,7 @@ def main():
             assert not np.isnan(u_by_gid[sg]).any(), "some global cells are owned by no rank"
             rel, _, mism = assert_state_close(u_by_gid[sg], u_ref_by_gid[sg], what=f"{world}-rank floodplain")
             assert abs(cmax.item() - oracle.courant()) <= 1e-12 * oracle.courant(), "max Courant number differs"
-            print(f"MULTIGPU_PARITY ok ranks={world} hr={args.hr} kernel={args.kernel} steps={args.steps} max_rel={rel:.2e} wetdry_mismatch={mism} "
+            print(f"MULTIGPU_PARITY ok ranks={world} p2p={args.p2p} hr={args.hr} kernel={args.kernel} steps={args.steps} max_rel={rel:.2e} wetdry_mismatch={mism} "
                   f"mass_drift={(m1.item() - m0.item()) / m0.item():.2e} courant={cmax.item():.4f}", flush=True)
         except AssertionError as exc:
             ok = False

@@ -34,6 +34,14 @@ def test_two_ranks_nccl_halo_matches_serial_oracle(kernel, tile):
     _run(2, ["--kernel", str(kernel), "--tile", str(tile)], 29517 + kernel)
 
 
+@pytest.mark.parametrize("kernel,tile", [(0, 0), (3, 224)])
+def test_two_ranks_peer_memory_halo_matches_serial_oracle(kernel, tile):
+    """The Euler fast path: border cells are written straight into the neighbour's ghost slots over NVLink (CUDA IPC)."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, ["--p2p", "--kernel", str(kernel), "--tile", str(tile), "--steps", "80"], 29551 + kernel)
+
+
 def test_two_ranks_hydrostatic_reconstruction():
     if _ngpus() < 2:
         pytest.skip("needs 2 GPUs")
@@ -43,4 +51,4 @@ def test_two_ranks_hydrostatic_reconstruction():
 def test_four_ranks_2x2_blocks():
     if _ngpus() < 4:
         pytest.skip("needs 4 GPUs")
-    _run(4, ["--kernel", "3", "--tile", "224", "--nx", "128", "--ny", "96"], 29541)
+    _run(4, ["--p2p", "--kernel", "3", "--tile", "224", "--nx", "128", "--ny", "96"], 29541)
