@@ -143,6 +143,8 @@ int rdyb_operator_get_boundary_fluxes(RdybOperator op, int32_t boundary_index, i
 /* Get/RestoreOperatorDomainExternalSource, src/operator.c:1394-1429: one component, owned order */
 int rdyb_operator_set_external_source(RdybOperator op, int32_t component, int32_t num_owned, const double *values);
 int rdyb_operator_get_external_source(RdybOperator op, int32_t component, int32_t num_owned, double *values);
+/* the whole external_sources Vec at once: AoS values[3*i + c] in owned order (src/operator.c:93-96) */
+int rdyb_operator_set_external_source_aos(RdybOperator op, int32_t num_owned, const double *values);
 /* Get/RestoreOperatorRegionalExternalSource, src/operator.c:1203-1241: values[i] -> owned cell owned_cell_ids[i] */
 int rdyb_operator_set_regional_external_source(RdybOperator op, int32_t component, int32_t n, const int32_t *owned_cell_ids, const double *values);
 /* Get/RestoreOperatorDomainMaterialProperties (Manning's n), src/operator.c:1435-1464 */

@@ -208,7 +208,9 @@ static int operator_create_impl(RdybOperator op, const RdybConfig *config, const
   CU(cudaEventCreate(&op->ev_t1));
   const size_t S = (size_t)L.stride;
   RDYB_CALL(dalloc(&op->state[0], 3 * S)); RDYB_CALL(dalloc(&op->state[1], 3 * S)); RDYB_CALL(dalloc(&op->F, 3 * S));
-  RDYB_CALL(dalloc(&op->src, 3 * S)); RDYB_CALL(dalloc(&op->mann, S)); RDYB_CALL(dalloc(&op->stage, 3 * S));
+  RDYB_CALL(dalloc(&op->src, 3 * S)); RDYB_CALL(dalloc(&op->mann, S));
+  /* the staging buffer also receives u_local in the VIEW's cell order, which may hold cells the layout dropped (non-face ghosts) */
+  RDYB_CALL(dalloc(&op->stage, 3 * (S > (size_t)L.num_view_cells ? S : (size_t)L.num_view_cells)));
   RDYB_CALL(dalloc(&op->stage_idx, S));
   RDYB_CALL(upload(&op->inv_area, L.inv_area, S)); RDYB_CALL(upload(&op->area, L.area, S));
   RDYB_CALL(upload(&op->dzdx, L.dzdx, S)); RDYB_CALL(upload(&op->dzdy, L.dzdy, S));
@@ -385,6 +387,21 @@ extern "C" int rdyb_operator_set_external_source(RdybOperator op, int32_t compon
   CU(cudaSetDevice(op->device));
   if (component > 0) op->mom_src = true;
   return upload_owned_component(op, values, op->src + (size_t)component * op->stride);
+}
+/* the Operator's external_sources Vec as it is: AoS [num_owned][3] in owned order (src/operator.c:93-96) */
+extern "C" int rdyb_operator_set_external_source_aos(RdybOperator op, int32_t num_owned, const double *values) {
+  RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(num_owned == op->N, RDYB_ERR_USER, "Wrong size (%d) for owned cell data (should be %d)", num_owned, op->N);
+  CU(cudaSetDevice(op->device));
+  bool mom = false;
+  for (int64_t i = 0; i < op->N && !mom; ++i) mom = values[3 * i + 1] != 0.0 || values[3 * i + 2] != 0.0;
+  op->mom_src = mom;
+  CU(cudaMemcpyAsync(op->stage, values, sizeof(double) * 3 * op->N, cudaMemcpyHostToDevice, op->stream));
+  aos_to_soa_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_owned, op->src, op->N, op->stride);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
 }
 extern "C" int rdyb_operator_get_external_source(RdybOperator op, int32_t component, int32_t num_owned, double *values) {
   RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
@@ -692,7 +709,7 @@ extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double
   RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
   /* u_local (AoS, view order, ghosts included) -> device SoA */
-  CU(cudaMemcpyAsync(op->stage, u_local, sizeof(double) * 3 * op->NL, cudaMemcpyHostToDevice, op->stream));
+  CU(cudaMemcpyAsync(op->stage, u_local, sizeof(double) * 3 * (size_t)op->L.num_view_cells, cudaMemcpyHostToDevice, op->stream));
   aos_to_soa_kernel<<<grid_for(op->NL, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_local, op->state[op->cur], op->NL, op->stride);
   LAUNCHED();
   CU(cudaGetLastError());

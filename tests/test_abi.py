@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _declared(header):
     txt = open(os.path.join(ROOT, "include", header)).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-    return sorted(set(re.findall(r"\b((?:rdyb|RDyB200|PetscOperatorB200|CreateB200)\w*)\s*\(", txt)))
+    return sorted(set(re.findall(r"\b((?:rdyb_|RDy[A-Z])\w*)\s*\(", txt)))
 
 
 @pytest.mark.parametrize("header", [h for h in sorted(os.listdir(os.path.join(ROOT, "include"))) if h.endswith(".h")])
