@@ -1,0 +1,129 @@
+"""Config B of BASELINE.json: manufactured-solution convergence (driver/mms.c, driver/tests/swe_roe/mms_conv_study.yaml)
+on the reference's own base mesh share/meshes/mms_triangles_dx1.exo (fixture tests/golden/mms_triangles_dx1.npz),
+regularly refined.  Every step the time-dependent source terms and Dirichlet values are set at t + dt/2 (MMSPreStep,
+src/rdymms.c:138-152), then one Euler step runs.
+
+CPU: the oracle (the reference's swe_petsc.c) reproduces the reference's convergence thresholds.
+GPU: the CUDA path, driven through RDyCreate/RDySetup/RDyAdvance + the rdycore.h setters, gives the same error norms as the
+oracle at each refinement level (relative 1e-9 on norms of ~1e-5 quantities) and the same states within the parity tolerance.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from rdycore_b200 import cases, mms, rdy
+from rdycore_b200.mesh import HostMesh
+
+from util import assert_state_close, make_oracle
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FORMS = mms.Forms()
+DT, NSTEPS = 0.01, 500  # time.time_step, time.stop / time_step
+
+
+def mms_case(level: int) -> cases.Case:
+    fx = np.load(os.path.join(HERE, "golden", "mms_triangles_dx1.npz"))
+    cells = fx["cells"]
+    mesh = HostMesh.from_cells(fx["xyz"], np.arange(0, 3 * len(cells) + 1, 3, dtype=np.int32), cells.ravel())
+    for _ in range(level):  # -dm_refine <level>
+        mesh = mesh.refine_triangles()
+    v = mesh.vertices()
+    mesh.set_vertex_z(FORMS.z(v[:, 0], v[:, 1]))  # SnapVerticesToBathymetry, src/rdymms.c:108-134
+    bnd = cases.boundaries_from_predicates(mesh, [(1, "domain_boundary", cases.DIRICHLET, lambda x, y: np.ones_like(x, dtype=bool))])
+    n = mesh.num_owned_cells
+    x, y = mesh.array("cell_xc")[:n], mesh.array("cell_yc")[:n]
+    u0 = FORMS.solution(x, y, 0.0)
+    case = cases.Case(f"mms_level{level}", mesh, cases.make_config(), bnd, u0, FORMS.mannings(x, y), np.zeros((n, 3)), DT)
+    be = bnd[0].edge_ids
+    case.info.update(x=x, y=y, xe=mesh.array("edge_xc")[be], ye=mesh.array("edge_yc")[be], areas=mesh.view_arrays()["cell_areas"][:n].copy())
+    return case
+
+
+def run_oracle(case, nsteps=NSTEPS):
+    oracle = make_oracle(case)
+    i = case.info
+    for k in range(nsteps):
+        t = k * DT + 0.5 * DT
+        oracle.array("boundary_values", 0)[:] = FORMS.solution(i["xe"], i["ye"], t).ravel()
+        oracle.array("external_sources")[:] = FORMS.sources(i["x"], i["y"], t).ravel()
+        oracle.step_euler(DT, 1)
+    return oracle.array("u_global").reshape(-1, 3).copy()
+
+
+def run_gpu(case, nsteps=NSTEPS):
+    rdy.RDyInit()
+    r = rdy.RDy(os.path.join(HERE, "decks", "mms.yaml"))
+    arr, nb = case.boundary_views()
+    r.set_mesh(case.mesh, arr, nb)
+    r.RDySetup()
+    r.RDySetDomainManningsN(case.mannings)  # RDyMMSUpdateMaterialProperties
+    r.RDySetInitialConditions(case.u0)
+    i = case.info
+    ne = len(i["xe"])
+    for k in range(nsteps):
+        t = r.RDyGetTime() + 0.5 * r.RDyGetTimeStep()
+        r.RDySetFlowDirichletBoundaryValues(0, ne, 3, FORMS.solution(i["xe"], i["ye"], t))
+        s = FORMS.sources(i["x"], i["y"], t)
+        r.RDySetDomainWaterSource(s[:, 0])
+        r.RDySetDomainXMomentumSource(s[:, 1])
+        r.RDySetDomainYMomentumSource(s[:, 2])
+        r.RDyAdvance()  # coupling_interval == time_step: one step
+    assert r.RDyGetStep() == nsteps
+    if nsteps == NSTEPS:
+        assert r.RDyFinished()
+    u = r.state()
+    r.RDyDestroy()
+    return u
+
+
+def test_base_mesh_fixture_is_the_reference_mesh():
+    case = mms_case(0)
+    assert case.mesh.num_owned_cells == 100 and case.mesh.num_vertices == 61 and case.mesh.num_boundary_edges == 20
+    assert np.isclose(case.info["areas"].sum(), 25.0)
+    assert mms_case(1).mesh.num_owned_cells == 400
+
+
+def test_oracle_meets_the_reference_convergence_thresholds():
+    """mms.convergence: base_refinement 1, num_refinements 3 -> levels 1..4; rates must exceed expected_rates."""
+    levels = [1, 2, 3, 4]
+    ncells, norms = [], []
+    for lv in levels:
+        case = mms_case(lv)
+        u = run_oracle(case)
+        i = case.info
+        norms.append(mms.error_norms(u, FORMS.solution(i["x"], i["y"], NSTEPS * DT), i["areas"]))
+        ncells.append(case.mesh.num_owned_cells)
+    for c, name in enumerate(("h", "hu", "hv")):
+        for k, norm_name in enumerate(("L1", "L2", "Linf")):
+            rate = mms.convergence_rates(ncells, [[n[k][c]] for n in norms])[0]
+            assert rate > mms.EXPECTED_RATES[name][k], f"{norm_name} convergence rate for {name} is {rate} (expected {mms.EXPECTED_RATES[name][k]})"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("level", [1, 2, 3])
+def test_cuda_path_matches_the_oracle_on_the_mms_problem(level):
+    case = mms_case(level)
+    u_ref = run_oracle(case)
+    u = run_gpu(case)
+    assert_state_close(u, u_ref, what=f"MMS level {level}")
+    i = case.info
+    exact = FORMS.solution(i["x"], i["y"], NSTEPS * DT)
+    for a, b in zip(mms.error_norms(u, exact, i["areas"]), mms.error_norms(u_ref, exact, i["areas"])):
+        assert np.allclose(a, b, rtol=1e-9, atol=0.0)
+
+
+@pytest.mark.gpu
+def test_cuda_path_meets_the_reference_convergence_thresholds():
+    levels = [1, 2, 3, 4]
+    ncells, norms = [], []
+    for lv in levels:
+        case = mms_case(lv)
+        u = run_gpu(case)
+        i = case.info
+        norms.append(mms.error_norms(u, FORMS.solution(i["x"], i["y"], NSTEPS * DT), i["areas"]))
+        ncells.append(case.mesh.num_owned_cells)
+    for c, name in enumerate(("h", "hu", "hv")):
+        for k in range(3):
+            rate = mms.convergence_rates(ncells, [[n[k][c]] for n in norms])[0]
+            assert rate > mms.EXPECTED_RATES[name][k]
