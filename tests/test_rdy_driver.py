@@ -190,10 +190,12 @@ def test_adaptive_time_step_follows_the_reference_rule():
     """src/rdyadvance.c:303-343: dt is rescaled at the start of every RDyAdvance from the Courant number of the last
     right-hand-side evaluation of the previous one.  (That evaluation may be the shortened last step of the interval, whose
     small dt gives a small Courant number and lets dt grow beyond the target: reference behaviour, mirrored as it is.)"""
-    case = cases.floodplain(nx=40, ny=36, eta0=9.0, hr=True)
-    r = _make("adaptive_hr.yaml", case)
+    # a fully wet case: with wet/dry fronts a 1e-15 relative change of dt moves the state by 1e-8 (measured with the oracle),
+    # which would test chaos, not the time loop
+    case = cases.dam_break_quads(nx=40, ny=40, source_method=cases.SEMI_IMPLICIT)
+    r = _make("adaptive.yaml", case)
     oracle = make_oracle(case)
-    target, max_inc, dt, interval, stop = 0.3, 2.0, 0.00016666666666666666 * 60, 0.08333333333333333 * 60, 0.5 * 60.0
+    target, max_inc, dt, interval, stop = 0.3, 2.0, 0.0002, 0.02, 0.12
     t, courant, dts = 0.0, None, []
     while not r.RDyFinished():
         r.RDyAdvance()
