@@ -26,6 +26,9 @@ struct TiledDev {
   uint32_t *edge_lr;
   double *edge_sn, *edge_cn, *edge_len;
   uint16_t *cell_edges;
+  /* optional launch order (pipelined host-Vec apply): positions [sub_begin, sub_end) of `order` name the tiles to run */
+  const int32_t *order;
+  int32_t sub_begin, sub_end;
 };
 
 struct TiledArgs {
@@ -36,6 +39,7 @@ struct TiledArgs {
   const uint32_t *__restrict__ edge_lr;
   const double *__restrict__ edge_sn, *__restrict__ edge_cn, *__restrict__ edge_len;
   const uint16_t *__restrict__ cell_edges;
+  const int32_t *__restrict__ tile_order; /* NULL: tiles run in index order; else launch position -> tile (K3, K4) */
   int32_t tile0;      /* first tile of this launch */
   int32_t max_cells;  /* shared-memory capacities */
   int32_t max_staged; /* tile cells + halo cells */

@@ -116,8 +116,9 @@ __global__ void __launch_bounds__(RDYB_ASYNC_THREADS, 2) swe_tiled_async_kernel(
       const int s = it & 1;
       mbar_wait(&empty_bar[s], ((it >> 1) & 1) ^ 1);
       const StageView v = stage_view<HR>(smem_raw + (size_t)s * q.stage_bytes, TC, CS, ME);
-      const int4 d0 = *reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tile);
-      const int2 d1 = *reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tile + 4);
+      const int tn = p.tile_order ? __ldg(p.tile_order + tile) : tile; /* launch position -> tile */
+      const int4 d0 = *reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tn);
+      const int2 d1 = *reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tn + 4);
       const int cb = d0.x, ncell = d0.y, eo = d0.z, nedge = d0.w, ho = d1.x, nhalo = d1.y;
       if (lane == 0) {
         v.desc[0] = cb; v.desc[1] = ncell; v.desc[2] = eo; v.desc[3] = nedge; v.desc[4] = ho; v.desc[5] = nhalo;
@@ -336,6 +337,8 @@ static inline int tiled_async_launch(const TiledDev &d, const RdybTiledLayout &T
   p.tile0 = 0; p.max_cells = T.tile_cells; p.max_staged = 0; p.max_edges = 0;
   q.tile_begin = a.begin < n_interior ? 0 : T.num_interior_tiles;
   q.tile_end = (a.end <= n_interior && a.begin < n_interior) ? T.num_interior_tiles : T.num_tiles;
+  p.tile_order = d.order;
+  if (d.order) { if (d.sub_begin > q.tile_begin) q.tile_begin = d.sub_begin; if (d.sub_end < q.tile_end) q.tile_end = d.sub_end; }
   if (q.tile_end <= q.tile_begin) return RDYB_SUCCESS;
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;

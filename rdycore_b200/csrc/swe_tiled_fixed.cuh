@@ -90,13 +90,16 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
     int tile = q.tile_begin + blockIdx.x;
     int4 d0 = make_int4(0, 0, 0, 0), n0 = d0;
     int2 d1 = make_int2(0, 0), n1 = d1;
+    const int32_t *ord = p.tile_order; /* launch position -> tile, or NULL */
     if (tile < q.tile_end) {
-      d0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tile));
-      d1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tile + 4));
+      const int tn = ord ? __ldg(ord + tile) : tile;
+      d0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tn));
+      d1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tn + 4));
     }
     if (tile + G < q.tile_end) {
-      n0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)(tile + G)));
-      n1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)(tile + G) + 4));
+      const int tn = ord ? __ldg(ord + tile + G) : tile + G;
+      n0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tn));
+      n1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tn + 4));
     }
     int hidx[HK];
 #pragma unroll
@@ -107,8 +110,9 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       int4 nn0 = make_int4(0, 0, 0, 0);
       int2 nn1 = make_int2(0, 0);
       if (tile + 2 * G < q.tile_end) {
-        nn0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)(tile + 2 * G)));
-        nn1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)(tile + 2 * G) + 4));
+        const int tn = ord ? __ldg(ord + tile + 2 * G) : tile + 2 * G;
+        nn0 = __ldg(reinterpret_cast<const int4 *>(p.tile_desc + 8 * (size_t)tn));
+        nn1 = __ldg(reinterpret_cast<const int2 *>(p.tile_desc + 8 * (size_t)tn + 4));
       }
       int nh[HK];
 #pragma unroll
@@ -382,6 +386,8 @@ static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T
   { const char *dbg = getenv("RDYB_DEBUG_COPYONLY"); if (dbg && dbg[0] == '1') p.tile0 = 1; }
   q.tile_begin = a.begin < n_interior ? 0 : T.num_interior_tiles;
   q.tile_end = (a.end <= n_interior && a.begin < n_interior) ? T.num_interior_tiles : T.num_tiles;
+  p.tile_order = d.order;
+  if (d.order) { if (d.sub_begin > q.tile_begin) q.tile_begin = d.sub_begin; if (d.sub_end < q.tile_end) q.tile_end = d.sub_end; }
   if (q.tile_end <= q.tile_begin) return RDYB_SUCCESS;
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
