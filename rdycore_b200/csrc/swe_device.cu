@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <algorithm>
 #include <vector>
 
 #include "device_layout.h"
@@ -128,6 +129,18 @@ struct RdybOperator_ {
   /* timing of the last step_euler call */
   double last_ms = 0.0;
   int32_t last_launches = 0;
+  /* pipelined host-Vec apply (rdyb_operator_apply_host): u_local is uploaded in chunks of view cells; a tile runs as soon as every
+   * cell it reads has arrived, and a range of F goes back to the host as soon as every tile that writes into it has run, so the
+   * host->device and device->host copies overlap (PCIe is full duplex) instead of running one after the other */
+  struct HostPipe {
+    bool built = false, usable = false;
+    int32_t tile_cells = 0, nchunks = 0, chunk_cells = 0, out_cells = 0;
+    int32_t *order = nullptr, *local_to_dev = nullptr, *owned_to_dev = nullptr; /* device */
+    double *stage_in = nullptr, *stage_out = nullptr;                           /* device */
+    std::vector<int32_t> gi, gf, out_need; /* launch-order group offsets (interior / frontier tiles), group an F range waits for */
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    std::vector<cudaEvent_t> ev_in, ev_out;
+  } pipe;
 };
 
 template <typename T>
@@ -161,6 +174,12 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
                   op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y};
   for (void *p : ptrs)
     if (p) cudaFree(p);
+  for (void *p : {(void *)op->pipe.order, (void *)op->pipe.local_to_dev, (void *)op->pipe.owned_to_dev, (void *)op->pipe.stage_in, (void *)op->pipe.stage_out})
+    if (p) cudaFree(p);
+  for (cudaEvent_t e : op->pipe.ev_in) cudaEventDestroy(e);
+  for (cudaEvent_t e : op->pipe.ev_out) cudaEventDestroy(e);
+  if (op->pipe.s_in) cudaStreamDestroy(op->pipe.s_in);
+  if (op->pipe.s_out) cudaStreamDestroy(op->pipe.s_out);
   tiled_dev_free(&op->td);
   warp_dev_free(&op->wd);
   rdyb_warp_layout_free(&op->WL);
@@ -278,6 +297,7 @@ extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_
   return RDYB_SUCCESS;
 }
 
+static void pipe_release(RdybOperator op);
 /* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
@@ -288,6 +308,7 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
       tiled_dev_free(&op->td);
       rdyb_tiled_layout_free(&op->T);
       op->has_tiled = false;
+      pipe_release(op);
     }
     if (!op->has_tiled) {
       RDYB_CALL(rdyb_tiled_layout_build(&op->L, tile_cells, &op->T));
@@ -705,9 +726,127 @@ static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool eu
   return RDYB_SUCCESS;
 }
 
+/* ---------------- pipelined host-Vec apply ---------------- */
+static void pipe_release(RdybOperator op) {
+  auto &P = op->pipe;
+  for (void *p : {(void *)P.order, (void *)P.local_to_dev, (void *)P.owned_to_dev, (void *)P.stage_in, (void *)P.stage_out})
+    if (p) cudaFree(p);
+  P.order = P.local_to_dev = P.owned_to_dev = nullptr; P.stage_in = P.stage_out = nullptr;
+  P.built = P.usable = false;
+}
+
+/* launch order and readiness groups for the current tiled layout (host work, once per layout) */
+static int pipe_build(RdybOperator op) {
+  auto &P = op->pipe;
+  pipe_release(op);
+  P.built = true; P.tile_cells = op->T.tile_cells;
+  const RdybLayout &L = op->L;
+  const RdybTiledLayout &T = op->T;
+  const int64_t nview = L.num_view_cells;
+  const char *env = getenv("RDYB_HOST_PIPELINE"); /* "0" switches the pipeline off, a number sets the chunk count */
+  int want = env ? atoi(env) : 16;
+  const char *env_min = getenv("RDYB_HOST_PIPELINE_MIN_CELLS"); /* tests lower it to exercise the pipeline on small meshes */
+  const int64_t min_cells = env_min ? atoll(env_min) : 262144;
+  if (want <= 1 || nview < min_cells || op->N < min_cells || op->N < want) return RDYB_SUCCESS; /* small meshes: the copies are too short to overlap */
+  if (want > 64) want = 64;
+  P.nchunks = want;
+  P.chunk_cells = (int32_t)((nview + want - 1) / want);
+  P.out_cells = (op->N + want - 1) / want;
+  const int nt = T.num_tiles, nit = T.num_interior_tiles;
+  std::vector<int32_t> ready((size_t)nt, 0), tile_of((size_t)op->N, 0);
+  for (int t = 0; t < nt; ++t) {
+    const int32_t *d = T.tile_desc + 8 * (size_t)t;
+    int r = 0;
+    for (int32_t c = d[0]; c < d[0] + d[1]; ++c) { const int k = L.dev_to_local[c] / P.chunk_cells; if (k > r) r = k; tile_of[c] = t; }
+    for (int32_t h = d[4]; h < d[4] + d[5]; ++h) { const int k = L.dev_to_local[T.halo_cells[h]] / P.chunk_cells; if (k > r) r = k; }
+    ready[t] = r;
+  }
+  /* counting sort of the interior tiles, then of the frontier tiles, by the chunk that completes their inputs */
+  std::vector<int32_t> order((size_t)nt);
+  P.gi.assign((size_t)want + 1, 0); P.gf.assign((size_t)want + 1, 0);
+  for (int t = 0; t < nit; ++t) ++P.gi[(size_t)ready[t] + 1];
+  for (int t = nit; t < nt; ++t) ++P.gf[(size_t)ready[t] + 1];
+  for (int c = 0; c < want; ++c) { P.gi[c + 1] += P.gi[c]; P.gf[c + 1] += P.gf[c]; }
+  {
+    std::vector<int32_t> ci(P.gi.begin(), P.gi.end() - 1), cf(P.gf.begin(), P.gf.end() - 1);
+    for (int t = 0; t < nit; ++t) order[(size_t)ci[ready[t]]++] = t;
+    for (int t = nit; t < nt; ++t) order[(size_t)nit + cf[ready[t]]++] = t;
+  }
+  for (int c = 0; c <= want; ++c) P.gf[c] += nit; /* absolute launch positions */
+  const int nout = (op->N + P.out_cells - 1) / P.out_cells;
+  P.out_need.assign((size_t)nout, 0);
+  for (int32_t o = 0; o < op->N; ++o) {
+    const int r = ready[tile_of[L.owned_to_dev[o]]];
+    int32_t &need = P.out_need[(size_t)(o / P.out_cells)];
+    if (r > need) need = r;
+  }
+  RDYB_CALL(upload(&P.order, order.data(), (size_t)nt));
+  RDYB_CALL(upload(&P.local_to_dev, L.local_to_dev, (size_t)nview));
+  RDYB_CALL(upload(&P.owned_to_dev, L.owned_to_dev, (size_t)op->N));
+  RDYB_CALL(dalloc(&P.stage_in, 3 * (size_t)nview));
+  RDYB_CALL(dalloc(&P.stage_out, 3 * (size_t)op->N));
+  if (!P.s_in) { CU(cudaStreamCreateWithFlags(&P.s_in, cudaStreamNonBlocking)); CU(cudaStreamCreateWithFlags(&P.s_out, cudaStreamNonBlocking)); }
+  while ((int)P.ev_in.size() < want) { cudaEvent_t e; CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); P.ev_in.push_back(e); }
+  while ((int)P.ev_out.size() < nout) { cudaEvent_t e; CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); P.ev_out.push_back(e); }
+  P.usable = true;
+  return RDYB_SUCCESS;
+}
+
+static int apply_host_pipelined(RdybOperator op, double dt, const double *u_local, double *f_global) {
+  auto &P = op->pipe;
+  const int64_t nview = op->L.num_view_cells;
+  double *state = op->state[op->cur];
+  const int nout = (int)P.out_need.size();
+  int kout = 0;
+  ncclComm_t saved = op->comm;
+  op->comm = nullptr; /* ghosts come from the caller */
+  int ierr = RDYB_SUCCESS;
+  auto body = [&]() -> int {
+    for (int c = 0; c < P.nchunks; ++c) {
+      const int64_t c0 = (int64_t)c * P.chunk_cells;
+      const int32_t n = (int32_t)std::min<int64_t>(P.chunk_cells, nview - c0);
+      if (n > 0) {
+        CU(cudaMemcpyAsync(P.stage_in + 3 * c0, u_local + 3 * c0, sizeof(double) * 3 * (size_t)n, cudaMemcpyHostToDevice, P.s_in));
+        CU(cudaEventRecord(P.ev_in[c], P.s_in));
+        CU(cudaStreamWaitEvent(op->stream, P.ev_in[c], 0));
+        aos_scatter_soa_kernel<<<grid_for(n, 256), 256, 0, op->stream>>>(P.stage_in + 3 * c0, P.local_to_dev + c0, state, n, op->stride);
+        LAUNCHED();
+        CU(cudaGetLastError());
+      }
+      op->td.order = P.order;
+      if (P.gi[c + 1] > P.gi[c]) { op->td.sub_begin = P.gi[c]; op->td.sub_end = P.gi[c + 1]; RDYB_CALL(launch_cells(op, state, op->F, dt, false, 0, op->NI, 0)); }
+      if (P.gf[c + 1] > P.gf[c]) { op->td.sub_begin = P.gf[c]; op->td.sub_end = P.gf[c + 1]; RDYB_CALL(launch_cells(op, state, op->F, dt, false, op->NI, op->N, op->ncblocks_interior)); }
+      for (; kout < nout && P.out_need[kout] <= c; ++kout) {
+        const int64_t o0 = (int64_t)kout * P.out_cells;
+        const int32_t m = (int32_t)std::min<int64_t>(P.out_cells, op->N - o0);
+        soa_gather_aos_kernel<<<grid_for(m, 256), 256, 0, op->stream>>>(op->F, P.owned_to_dev + o0, P.stage_out + 3 * o0, m, op->stride);
+        LAUNCHED();
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(P.ev_out[kout], op->stream));
+        CU(cudaStreamWaitEvent(P.s_out, P.ev_out[kout], 0));
+        CU(cudaMemcpyAsync(f_global + 3 * o0, P.stage_out + 3 * o0, sizeof(double) * 3 * (size_t)m, cudaMemcpyDeviceToHost, P.s_out));
+      }
+    }
+    return RDYB_SUCCESS;
+  };
+  ierr = body();
+  op->td.order = nullptr; op->td.sub_begin = op->td.sub_end = 0;
+  op->comm = saved;
+  cudaStreamSynchronize(P.s_in);
+  cudaStreamSynchronize(op->stream);
+  cudaError_t e = cudaStreamSynchronize(P.s_out);
+  RDYB_CALL(ierr);
+  if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "CUDA error in the pipelined host-Vec apply (%s)", cudaGetErrorString(e));
+  return RDYB_SUCCESS;
+}
+
 extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double *u_local, double *f_global) {
   RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
+  if (op->kernel_kind >= 2 && op->kernel_kind <= 3 && op->has_tiled) { /* K3 / K4: chunked, overlapped copies */
+    if (!op->pipe.built || op->pipe.tile_cells != op->T.tile_cells) RDYB_CALL(pipe_build(op));
+    if (op->pipe.usable) return apply_host_pipelined(op, dt, u_local, f_global);
+  }
   /* u_local (AoS, view order, ghosts included) -> device SoA */
   CU(cudaMemcpyAsync(op->stage, u_local, sizeof(double) * 3 * (size_t)op->L.num_view_cells, cudaMemcpyHostToDevice, op->stream));
   aos_to_soa_kernel<<<grid_for(op->NL, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_local, op->state[op->cur], op->NL, op->stride);

@@ -204,6 +204,22 @@ __global__ void soa_to_aos_kernel(const double *__restrict__ src, const int32_t 
     dst[s] = src[d]; dst[s + 1] = src[stride + d]; dst[s + 2] = src[2 * stride + d];
   }
 }
+/* the same conversions walked in the HOST order (chunks of the pipelined host-Vec apply):
+ * dst SoA[c*stride + map[i]] = src AoS[3*i + c] (map[i] < 0: a view cell the layout dropped) and dst AoS[3*i + c] = src SoA[c*stride + map[i]] */
+__global__ void aos_scatter_soa_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n, int32_t stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const int d = map[i];
+    if (d >= 0) { dst[d] = src[3 * (size_t)i]; dst[stride + d] = src[3 * (size_t)i + 1]; dst[2 * stride + d] = src[3 * (size_t)i + 2]; }
+  }
+}
+__global__ void soa_gather_aos_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n, int32_t stride) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const int d = map[i];
+    dst[3 * (size_t)i] = src[d]; dst[3 * (size_t)i + 1] = src[stride + d]; dst[3 * (size_t)i + 2] = src[2 * stride + d];
+  }
+}
 /* dst[d] = src[map[d]] / dst[map[d]] = src[d] */
 __global__ void gather_kernel(const double *__restrict__ src, const int32_t *__restrict__ map, double *__restrict__ dst, int32_t n) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
