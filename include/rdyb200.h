@@ -183,6 +183,8 @@ int rdyb_operator_synchronize(RdybOperator op);
 /* ---- diagnostics: Reset/Update/GetOperatorDiagnostics, src/operator.c:757-768,867-893 ---- */
 int rdyb_operator_reset_diagnostics(RdybOperator op);
 int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics *diags); /* local max since reset (syncs) */
+/* UpdateOperatorDiagnostics, src/operator.c:867-885: max over the ranks of the NCCL communicator (collective); ids stay on the rank holding it */
+int rdyb_operator_get_courant_global(RdybOperator op, RdybCourantDiagnostics *diags);
 /* sum over owned cells of area*h (mass); deterministic two-stage reduction (syncs) */
 int rdyb_operator_get_mass(RdybOperator op, double *mass);
 

@@ -408,7 +408,7 @@ PetscErrorCode RDyAdvance(RDy rdy) {
   rdy->time = t_end;
   if (rdy->adaptive) { /* UpdateOperatorDiagnostics, :366-372: the one host sync of the interval */
     RdybCourantDiagnostics d;
-    RDYB_CALL(rdyb_operator_get_courant(rdy->op, &d));
+    RDYB_CALL(rdyb_operator_get_courant_global(rdy->op, &d)); /* all ranks take the same dt (MPI_Allreduce in the reference) */
     rdy->last_courant = d.max_courant_num;
     rdy->courant_valid = d.max_courant_num > 0.0;
   }

@@ -994,6 +994,23 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   return RDYB_SUCCESS;
 }
 
+/* UpdateOperatorDiagnostics (src/operator.c:867-885): the maximum over all ranks of the communicator.  The reference reduces
+ * {value, edge id, cell id} with a custom MPI op; here the value is reduced (ncclAllReduce, max) and the ids are kept on the
+ * rank(s) that hold the maximum, -1 elsewhere.  Collective when a communicator exists; the local result otherwise. */
+extern "C" int rdyb_operator_get_courant_global(RdybOperator op, RdybCourantDiagnostics *d) {
+  RDYB_CALL(rdyb_operator_get_courant(op, d));
+  if (!op->comm || op->nranks <= 1) return RDYB_SUCCESS;
+  double *scratch = op->partial; /* 1024 doubles of reduction scratch */
+  CU(cudaMemcpyAsync(scratch, &d->max_courant_num, sizeof(double), cudaMemcpyHostToDevice, op->stream));
+  NC(g_nccl.AllReduce(scratch, scratch + 1, 1, ncclDouble, ncclMax, op->comm, op->stream));
+  double global = 0.0;
+  CU(cudaMemcpyAsync(&global, scratch + 1, sizeof(double), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  if (global != d->max_courant_num) { d->global_edge_id = -1; d->global_cell_id = -1; }
+  d->max_courant_num = global;
+  return RDYB_SUCCESS;
+}
+
 extern "C" int rdyb_operator_get_mass(RdybOperator op, double *mass) {
   RDYB_CHECK(op && mass, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
