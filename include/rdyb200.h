@@ -44,6 +44,9 @@ enum { RDYB_SOURCE_SEMI_IMPLICIT = 0, RDYB_SOURCE_IMPLICIT_XQ2018 = 1 };
 enum { RDYB_WELL_BALANCING_NONE = 0, RDYB_WELL_BALANCING_BS2002 = 1, RDYB_WELL_BALANCING_HR = 2 };
 /* include/private/rdyconfigimpl.h:110-115 (RDyNumericsTemporal) */
 enum { RDYB_TEMPORAL_EULER = 0, RDYB_TEMPORAL_RK4 = 1 };
+/* config.numerics.second_order + limiter (include/private/rdyconfigimpl.h; resolved as in src/swe/swe_petsc.c:357-369):
+ * first order, or MUSCL reconstruction with the minmod (default), no, or van Leer limiter */
+enum { RDYB_RECON_FIRST_ORDER = 0, RDYB_RECON_MUSCL_MINMOD = 1, RDYB_RECON_MUSCL_NONE = 2, RDYB_RECON_MUSCL_VANLEER = 3 };
 
 /* Physics / numerics parameters the kernels read.  Filled from RDyConfig:
  * config.physics.flow.{tiny_h,h_anuga_regular,source.method,source.xq2018_threshold,well_balancing},
@@ -55,7 +58,7 @@ typedef struct {
   int32_t source_method;    /* RDYB_SOURCE_* */
   int32_t well_balancing;   /* RDYB_WELL_BALANCING_* */
   int32_t temporal;         /* RDYB_TEMPORAL_* */
-  int32_t reserved;
+  int32_t reconstruction;   /* RDYB_RECON_* (0 = first order) */
 } RdybConfig;
 
 /* A borrowed, read-only view of the RDyMesh arrays the path consumes
@@ -82,6 +85,9 @@ typedef struct {
   const double  *edge_cn, *edge_sn;   /* RDyEdges.cn, sn */
   const int32_t *internal_edge_ids;   /* RDyEdges.internal_edge_ids, length num_internal_edges */
   const int64_t *edge_global_ids;     /* RDyEdges.global_ids (may be NULL => local id) */
+  /* second order only (NULL otherwise): edge midpoints 0.5*(v0+v1) as ReconstructFaceValues forms them from
+   * RDyEdges.vertex_ids / RDyVertices.points (src/operator_fluxes_ceed.c:1162-1166); cell_xc/cell_yc are then required too */
+  const double  *edge_xm, *edge_ym;
 } RdybMeshView;
 
 /* One RDyBoundary (include/private/rdyboundaryimpl.h:9-16) with the flow

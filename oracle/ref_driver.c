@@ -29,12 +29,49 @@ PetscErrorCode CreatePetscTracerBoundaryFluxOperator(RDyMesh *m, const RDyConfig
                                                      OperatorDiagnostics *d, PetscOperator *o) UNREACHED("tracers")
 PetscErrorCode CreatePetscTracerSourceOperator(RDyMesh *m, const RDyConfig c, Vec e, Vec p, PetscOperator *o) UNREACHED("tracers")
 PetscErrorCode CreatePetscTracerSourceHROperator(RDyMesh *m, const RDyConfig c, Vec e, Vec p, PetscOperator *o) UNREACHED("tracers")
-PetscErrorCode PrecomputeLSGradCoeffs(MPI_Comm comm, RDyMesh *m, PetscReal *c) UNREACHED("MUSCL")
+
+/* ---- the four second-order helpers of src/operator_fluxes_ceed.c (a libCEED translation unit that cannot be built here),
+ * restated in muscl_helpers.h and bound to the reference's signatures so that the reference's own ApplyInteriorFlux2R
+ * (src/swe/swe_petsc.c:98-213) runs on top of them ---- */
+#include "muscl_helpers.h"
+static void mesh_xy(RDyMesh *m, double **xc, double **yc, double **xm, double **ym) {
+  *xc = malloc(sizeof(double) * (size_t)(m->num_cells + 1)); *yc = malloc(sizeof(double) * (size_t)(m->num_cells + 1));
+  for (PetscInt c = 0; c < m->num_cells; ++c) { (*xc)[c] = m->cells.centroids[c].X[0]; (*yc)[c] = m->cells.centroids[c].X[1]; }
+  if (!xm) return;
+  *xm = malloc(sizeof(double) * (size_t)(m->num_edges + 1)); *ym = malloc(sizeof(double) * (size_t)(m->num_edges + 1));
+  for (PetscInt e = 0; e < m->num_edges; ++e) { /* edge midpoint from its two vertices, :1162-1166 */
+    PetscInt v0 = m->edges.vertex_ids[2 * e], v1 = m->edges.vertex_ids[2 * e + 1];
+    (*xm)[e] = 0.5 * (m->vertices.points[v0].X[0] + m->vertices.points[v1].X[0]);
+    (*ym)[e] = 0.5 * (m->vertices.points[v0].X[1] + m->vertices.points[v1].X[1]);
+  }
+}
+PetscErrorCode PrecomputeLSGradCoeffs(MPI_Comm comm, RDyMesh *m, PetscReal *c) {
+  (void)comm;
+  double *xc, *yc;
+  mesh_xy(m, &xc, &yc, NULL, NULL);
+  int ierr = muscl_ls_coeffs(m->num_cells, m->num_internal_edges, m->edges.internal_edge_ids, m->edges.cell_ids, xc, yc, c);
+  free(xc); free(yc);
+  return ierr;
+}
 PetscErrorCode ComputeLeastSquaresGradients(RDyMesh *m, const PetscReal *c, const PetscScalar *u, PetscScalar *a, PetscScalar *b,
-                                            PetscScalar *d) UNREACHED("MUSCL")
-PetscErrorCode CommunicateCellGradients(DM dm, RDyMesh *m, PetscScalar *a, PetscScalar *b, PetscScalar *c) UNREACHED("MUSCL")
+                                            PetscScalar *d) {
+  muscl_gradients(m->num_cells, m->num_internal_edges, m->edges.internal_edge_ids, m->edges.cell_ids, c, u, a, b, d);
+  return 0;
+}
+/* serial: the owned -> ghost round trip leaves the gradients unchanged (:1049-1051) */
+PetscErrorCode CommunicateCellGradients(DM dm, RDyMesh *m, PetscScalar *a, PetscScalar *b, PetscScalar *c) {
+  (void)dm; (void)m; (void)a; (void)b; (void)c;
+  return 0;
+}
 PetscErrorCode ReconstructFaceValues(RDyMesh *m, const PetscScalar *u, const PetscScalar *a, const PetscScalar *b, const PetscScalar *c,
-                                     RDyLimiterType l, CeedScalar *q) UNREACHED("MUSCL")
+                                     RDyLimiterType l, CeedScalar *q) {
+  double *xc, *yc, *xm, *ym;
+  mesh_xy(m, &xc, &yc, &xm, &ym);
+  muscl_faces(m->num_internal_edges, m->edges.internal_edge_ids, m->edges.cell_ids, (const int32_t *)m->edges.is_owned, xc, yc, xm, ym, u, a, b,
+              c, (int)l, q);
+  free(xc); free(yc); free(xm); free(ym);
+  return 0;
+}
 
 struct SweOracle_ {
   RDyConfig        *config;
@@ -46,6 +83,7 @@ struct SweOracle_ {
   Operator          op; /* the reference's Operator struct; only the members ApplyPetscOperator touches are set */
   Vec               u_global, u_local, rhs;
   Vec               k[4], ystage; /* RK4 work vectors */
+  struct _shim_DM   dm;           /* serial DM behind u_local (second-order path) */
 };
 
 static Vec vec_new(PetscInt n, PetscInt bs) {
@@ -74,6 +112,8 @@ int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb,
   c->physics.flow.well_balancing          = (RDyWellBalanceMethod)cfg->well_balancing;
   c->numerics.riemann                     = RIEMANN_ROE;
   c->numerics.temporal                    = TEMPORAL_EULER;
+  c->numerics.second_order                = cfg->reconstruction != RDYB_RECON_FIRST_ORDER;
+  c->numerics.limiter = cfg->reconstruction == RDYB_RECON_MUSCL_NONE ? LIMITER_NONE : cfg->reconstruction == RDYB_RECON_MUSCL_VANLEER ? LIMITER_VANLEER : LIMITER_MINMOD;
 
   /* RDyMesh from the view: only the members the PETSc SWE operators read */
   RDyMesh *m = &o->mesh;
@@ -99,6 +139,26 @@ int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb,
     strcpy(c->grid.cell_elevation.file, "from-mesh-view");
     m->cells.centroids = calloc((size_t)mv->num_cells, sizeof(RDyPoint));
     for (PetscInt i = 0; i < mv->num_cells; ++i) m->cells.centroids[i].X[2] = mv->cell_zc[i];
+  }
+  if (c->numerics.second_order) {
+    /* what ApplyInteriorFlux2R and its helpers read: centroids, edge vertices (two synthetic vertices per edge, both AT the
+     * view's midpoint, so that 0.5*(v0+v1) reproduces it exactly), edge ownership (serial: every edge is owned) */
+    if (!mv->cell_xc || !mv->cell_yc || !mv->edge_xm || !mv->edge_ym) { fprintf(stderr, "ref_driver: second order needs centroids and edge midpoints\n"); return PETSC_ERR_USER; }
+    if (!m->cells.centroids) m->cells.centroids = calloc((size_t)mv->num_cells, sizeof(RDyPoint));
+    for (PetscInt i = 0; i < mv->num_cells; ++i) { m->cells.centroids[i].X[0] = mv->cell_xc[i]; m->cells.centroids[i].X[1] = mv->cell_yc[i]; }
+    size_t ne = (size_t)(mv->num_edges > 0 ? mv->num_edges : 1);
+    m->num_vertices     = 2 * mv->num_edges;
+    m->vertices.points  = calloc(2 * ne, sizeof(RDyPoint));
+    m->edges.vertex_ids = calloc(2 * ne, sizeof(PetscInt));
+    m->edges.is_owned   = calloc(ne, sizeof(PetscBool));
+    for (PetscInt e = 0; e < mv->num_edges; ++e) {
+      for (int k = 0; k < 2; ++k) {
+        m->edges.vertex_ids[2 * e + k] = 2 * e + k;
+        m->vertices.points[2 * e + k].X[0] = mv->edge_xm[e]; m->vertices.points[2 * e + k].X[1] = mv->edge_ym[e];
+      }
+      m->edges.is_owned[e] = PETSC_TRUE;
+    }
+    m->num_owned_internal_edges = mv->num_internal_edges;
   }
 
   o->nb         = nb;
@@ -152,6 +212,8 @@ int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb,
   o->u_global = vec_new(3 * N, 3);
   o->rhs      = vec_new(3 * N, 3);
   o->u_local  = vec_new(3 * mv->num_cells, 3);
+  o->dm = (struct _shim_DM){.n_local = mv->num_cells, .bs = 3, .is_owned = m->cells.is_owned, .local_to_owned = m->cells.local_to_owned};
+  o->u_local->dm = &o->dm;
   for (int i = 0; i < 4; ++i) o->k[i] = vec_new(3 * N, 3);
   o->ystage = vec_new(3 * N, 3);
   return 0;
@@ -171,6 +233,7 @@ void swe_oracle_destroy(SweOracle o) {
   vec_free(o->u_global); vec_free(o->rhs); vec_free(o->u_local); vec_free(o->ystage);
   for (int i = 0; i < 4; ++i) vec_free(o->k[i]);
   free(o->mesh.cells.global_ids); free(o->mesh.edges.global_ids); free(o->mesh.cells.centroids);
+  free(o->mesh.vertices.points); free(o->mesh.edges.vertex_ids); free(o->mesh.edges.is_owned);
   free(o->boundaries); free(o->conditions); free(o->flows); free(o->config);
   free(o);
 }

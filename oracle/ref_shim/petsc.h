@@ -117,8 +117,29 @@ static inline PetscErrorCode VecAXPY(Vec y, PetscScalar alpha, Vec x) {
   return 0;
 }
 static inline PetscErrorCode VecView(Vec v, void *viewer) { (void)v; (void)viewer; return 0; }
-/* only reached from the MUSCL (second-order) path, which the shim does not support */
-static inline PetscErrorCode DMGetLocalVector(DM dm, Vec *v) { (void)dm; *v = NULL; return 56; }
-static inline PetscErrorCode DMRestoreLocalVector(DM dm, Vec *v) { (void)dm; (void)v; return 56; }
-static inline PetscErrorCode DMLocalToGlobal(DM dm, Vec l, InsertMode m, Vec g) { (void)dm; (void)l; (void)m; (void)g; return 56; }
+/* Serial DM stand-in for the second-order path (ApplyInteriorFlux2R, src/swe/swe_petsc.c:170-210): a local vector of
+ * n_local blocks, and DMLocalToGlobal(ADD_VALUES) adding the owned rows of a local vector to the global one (the ghost rows
+ * would travel to their owners; a serial mesh has none). */
+struct _shim_DM {
+  PetscInt         n_local, bs;
+  const PetscBool *is_owned;
+  const PetscInt  *local_to_owned;
+};
+static inline PetscErrorCode DMGetLocalVector(DM dm, Vec *v) {
+  *v = calloc(1, sizeof(**v));
+  (*v)->n = dm->n_local * dm->bs; (*v)->bs = dm->bs; (*v)->dm = dm;
+  (*v)->a = calloc((size_t)((*v)->n > 0 ? (*v)->n : 1), sizeof(PetscScalar));
+  return 0;
+}
+static inline PetscErrorCode DMRestoreLocalVector(DM dm, Vec *v) { (void)dm; free((*v)->a); free(*v); *v = NULL; return 0; }
+static inline PetscErrorCode DMLocalToGlobal(DM dm, Vec l, InsertMode m, Vec g) {
+  for (PetscInt c = 0; c < dm->n_local; ++c) {
+    if (!dm->is_owned[c]) continue;
+    for (PetscInt k = 0; k < dm->bs; ++k) {
+      if (m == ADD_VALUES) g->a[dm->bs * dm->local_to_owned[c] + k] += l->a[dm->bs * c + k];
+      else g->a[dm->bs * dm->local_to_owned[c] + k] = l->a[dm->bs * c + k];
+    }
+  }
+  return 0;
+}
 #endif

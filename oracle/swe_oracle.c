@@ -18,6 +18,7 @@
  *   RHS callback                   src/rdysetup.c:1120-1139
  */
 #include "swe_oracle.h"
+#include "muscl_helpers.h"
 
 #include <math.h>
 #include <stdio.h>
@@ -43,6 +44,9 @@ struct SweOracle_ {
   double    *u_global, *u_local, *rhs, *ext, *mat, *fdiv, *prim, *src_inst;
   double    *k[4], *ystage;
   RdybCourantDiagnostics courant;
+  /* second order (MUSCL): limiter (-1 = first order), geometry, LS weights, work arrays */
+  int     limiter;
+  double *xc, *yc, *xm, *ym, *ls_coef, *gh, *ghu, *ghv, *qface;
 };
 
 const char *swe_oracle_kind(void) { return "port"; }
@@ -79,6 +83,17 @@ int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb,
     fprintf(stderr, "Only semi_implicit and implicit_xq2018 are supported in the PETSc version\n");
     return RDYB_ERR_USER;
   }
+  /* numerics.second_order: only the first-order (non-HR) interior operator has the MUSCL variant (swe_petsc.c:357-376, 404) */
+  o->limiter = -1;
+  if (cfg->reconstruction != RDYB_RECON_FIRST_ORDER && cfg->well_balancing != RDYB_WELL_BALANCING_HR) {
+    if (!mv->cell_xc || !mv->cell_yc || !mv->edge_xm || !mv->edge_ym) { fprintf(stderr, "swe_oracle: second order needs centroids and edge midpoints\n"); return RDYB_ERR_USER; }
+    o->limiter = cfg->reconstruction == RDYB_RECON_MUSCL_NONE ? MUSCL_LIMITER_NONE : cfg->reconstruction == RDYB_RECON_MUSCL_VANLEER ? MUSCL_LIMITER_VANLEER : MUSCL_LIMITER_MINMOD;
+    o->xc = dup_arr(mv->cell_xc, (size_t)o->nc, 8); o->yc = dup_arr(mv->cell_yc, (size_t)o->nc, 8);
+    o->xm = dup_arr(mv->edge_xm, (size_t)o->ne, 8); o->ym = dup_arr(mv->edge_ym, (size_t)o->ne, 8);
+    o->ls_coef = dup_arr(NULL, 4 * (size_t)o->nie, 8); o->qface = dup_arr(NULL, 6 * (size_t)o->nie, 8);
+    o->gh = dup_arr(NULL, 2 * (size_t)o->nc, 8); o->ghu = dup_arr(NULL, 2 * (size_t)o->nc, 8); o->ghv = dup_arr(NULL, 2 * (size_t)o->nc, 8);
+    if (muscl_ls_coeffs(o->nc, o->nie, o->iedges, o->ecells, o->xc, o->yc, o->ls_coef)) return RDYB_ERR_MEM;
+  }
   o->bnd = calloc((size_t)(nb > 0 ? nb : 1), sizeof(OBoundary));
   for (int32_t b = 0; b < nb; ++b) {
     OBoundary *B = &o->bnd[b];
@@ -109,6 +124,7 @@ void swe_oracle_destroy(SweOracle o) {
   free(o->u_global); free(o->u_local); free(o->rhs); free(o->ext); free(o->mat); free(o->fdiv); free(o->prim); free(o->src_inst);
   free(o->ystage);
   for (int i = 0; i < 4; ++i) free(o->k[i]);
+  free(o->xc); free(o->yc); free(o->xm); free(o->ym); free(o->ls_coef); free(o->gh); free(o->ghu); free(o->ghv); free(o->qface);
   free(o);
 }
 
@@ -202,6 +218,37 @@ static void interior_flux(SweOracle o, double dt, const double *u, double *F) {
       if (o->is_owned[r]) F[3 * o->l2o[r] + d] += f[d] * (len / ar);
     }
   }
+}
+
+/* ApplyInteriorFlux2R, swe_petsc.c:98-213 (serial: every edge is owned, DMLocalToGlobal(ADD) adds the local vector's owned rows
+ * to the zeroed F; CommunicateCellGradients is the identity) */
+static void interior_flux_2r(SweOracle o, double dt, const double *u, double *F) {
+  const double tiny = o->cfg.tiny_h, ha = o->cfg.h_anuga_regular;
+  muscl_gradients(o->nc, o->nie, o->iedges, o->ecells, o->ls_coef, u, o->gh, o->ghu, o->ghv);
+  muscl_faces(o->nie, o->iedges, o->ecells, NULL, o->xc, o->yc, o->xm, o->ym, u, o->gh, o->ghu, o->ghv, o->limiter, o->qface);
+  double *loc = calloc(3 * (size_t)(o->nc > 0 ? o->nc : 1), sizeof(double)); /* rhs_local */
+  for (int32_t i = 0; i < o->nie; ++i) {
+    int32_t e = o->iedges[i], l = o->ecells[2 * e], r = o->ecells[2 * e + 1];
+    if (r < 0) continue;
+    const double *qf = &o->qface[6 * (size_t)i];
+    double hl = fmax(0.0, qf[0]), hr = fmax(0.0, qf[3]), ul, vl, ur, vr;
+    if (hr < tiny && hl < tiny) continue; /* computed then discarded by the reference (:155 vs :179) */
+    velocities(tiny, ha, hl, qf[1], qf[2], &ul, &vl);
+    velocities(tiny, ha, hr, qf[4], qf[5], &ur, &vr);
+    double f[3], amax;
+    roe_flux(hl, ul, vl, hr, ur, vr, o->sn[e], o->cn[e], f, &amax);
+    double len = o->len[e], al = o->area[l], ar = o->area[r];
+    double cnum = amax * len / fmin(al, ar) * dt;
+    courant_update(o, cnum, o->egid[e], al < ar ? o->cgid[l] : o->cgid[r]);
+    for (int d = 0; d < 3; ++d) {
+      loc[3 * l + d] += f[d] * (-len / al);
+      loc[3 * r + d] += f[d] * (len / ar);
+    }
+  }
+  for (int32_t c = 0; c < o->nc; ++c)
+    if (o->is_owned[c])
+      for (int d = 0; d < 3; ++d) F[3 * o->l2o[c] + d] += loc[3 * c + d];
+  free(loc);
 }
 
 /* swe_petsc.c:1000-1161 */
@@ -342,6 +389,7 @@ static int rhs_function(SweOracle o, double dt, const double *U, double *F) {
     if (o->is_owned[c]) memcpy(&o->u_local[3 * c], &U[3 * (size_t)o->l2o[c]], 3 * sizeof(double));
   o->courant.max_courant_num = 0.0; o->courant.global_edge_id = -1; o->courant.global_cell_id = -1;
   if (o->cfg.well_balancing == RDYB_WELL_BALANCING_HR) interior_flux_hr(o, dt, o->u_local, F);
+  else if (o->limiter >= 0) interior_flux_2r(o, dt, o->u_local, F);
   else interior_flux(o, dt, o->u_local, F);
   for (int32_t b = 0; b < o->nb; ++b) boundary_flux(o, &o->bnd[b], dt, o->u_local, F);
   memcpy(o->fdiv, F, 3 * N * sizeof(double));

@@ -23,7 +23,7 @@ class RdybConfig(C.Structure):
         ("source_method", C.c_int32),
         ("well_balancing", C.c_int32),
         ("temporal", C.c_int32),
-        ("reserved", C.c_int32),
+        ("reconstruction", C.c_int32),
     ]
 
 
@@ -48,6 +48,8 @@ class RdybMeshView(C.Structure):
         ("edge_sn", c_f64p),
         ("internal_edge_ids", c_i32p),
         ("edge_global_ids", c_i64p),
+        ("edge_xm", c_f64p),
+        ("edge_ym", c_f64p),
     ]
 
 

@@ -18,12 +18,14 @@ DIRICHLET, NEUMANN, REFLECTING, CRITICAL_OUTFLOW = 0, 1, 2, 3
 SEMI_IMPLICIT, IMPLICIT_XQ2018 = 0, 1
 WB_NONE, WB_BS2002, WB_HR = 0, 1, 2
 EULER, RK4 = 0, 1
+FIRST_ORDER, MUSCL_MINMOD, MUSCL_NONE, MUSCL_VANLEER = 0, 1, 2, 3  # numerics.second_order + limiter
 GRAVITY = 9.806
 
 
-def make_config(source_method=SEMI_IMPLICIT, well_balancing=WB_NONE, temporal=EULER, tiny_h=1e-7, h_anuga=0.0, xq2018_threshold=1e-10):
+def make_config(source_method=SEMI_IMPLICIT, well_balancing=WB_NONE, temporal=EULER, tiny_h=1e-7, h_anuga=0.0, xq2018_threshold=1e-10,
+                reconstruction=FIRST_ORDER):
     """Defaults of src/yaml_input.c:854-865."""
-    return RdybConfig(tiny_h, h_anuga, xq2018_threshold, source_method, well_balancing, temporal, 0)
+    return RdybConfig(tiny_h, h_anuga, xq2018_threshold, source_method, well_balancing, temporal, reconstruction)
 
 
 @dataclass

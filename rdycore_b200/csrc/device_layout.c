@@ -56,6 +56,7 @@ void rdyb_layout_free(RdybLayout *L) {
   free(L->dzdx); free(L->dzdy); free(L->zc); free(L->ell_nbr); free(L->ell_sn); free(L->ell_cn); free(L->ell_slen); free(L->ell_edge);
   free(L->b_offsets); free(L->b_type); free(L->b_cell); free(L->peer_ranks); free(L->send_offsets); free(L->send_cells);
   free(L->recv_offsets);
+  free(L->ell_gcx); free(L->ell_gcy); free(L->ell_dxs); free(L->ell_dys); free(L->ell_dxn); free(L->ell_dyn);
   memset(L, 0, sizeof(*L));
 }
 
@@ -235,6 +236,57 @@ fail:
   free(keys); free(frontier); free(placed); free(fill);
   rdyb_layout_free(L);
   return ierr;
+}
+
+/* ---------------- second-order (MUSCL) slot geometry ---------------- */
+/* Weighted least-squares gradient weights and face offsets per ELL slot.  Follows PrecomputeLSGradCoeffs
+ * (src/operator_fluxes_ceed.c:884-975): weight 1/d per neighbour, per-cell normal matrix summed over the local internal edges in
+ * internal_edge_ids order, analytic 2x2 inverse, |det| < 1e-15 => zero gradient; the left cell's weights are M_l^-1 (w dx, w dy),
+ * the right cell's M_r^-1 (w dx, w dy) with (dx, dy) = x_right - x_left for both. */
+int rdyb_layout_build_muscl(const RdybMeshView *mv, RdybLayout *L) {
+  RDYB_CHECK(mv->cell_xc && mv->cell_yc && mv->edge_xm && mv->edge_ym, RDYB_ERR_USER,
+             "second-order reconstruction needs cell centroids and edge midpoints in the mesh view");
+  const int32_t nc = mv->num_cells;
+  const size_t tot = (size_t)RDYB_ELL_WIDTH * (size_t)L->stride;
+  double *M = calloc(3 * (size_t)(nc > 0 ? nc : 1), sizeof(double)), *inv = calloc(4 * (size_t)(nc > 0 ? nc : 1), sizeof(double));
+  L->ell_gcx = calloc(tot, sizeof(double)); L->ell_gcy = calloc(tot, sizeof(double));
+  L->ell_dxs = calloc(tot, sizeof(double)); L->ell_dys = calloc(tot, sizeof(double));
+  L->ell_dxn = calloc(tot, sizeof(double)); L->ell_dyn = calloc(tot, sizeof(double));
+  if (!M || !inv || !L->ell_gcx || !L->ell_gcy || !L->ell_dxs || !L->ell_dys || !L->ell_dxn || !L->ell_dyn) {
+    free(M); free(inv);
+    return rdyb_fail(RDYB_ERR_MEM, "device layout: out of memory (MUSCL slot geometry)");
+  }
+  for (int32_t i = 0; i < mv->num_internal_edges; ++i) {
+    const int32_t e = mv->internal_edge_ids[i], l = mv->edge_cell_ids[2 * e], r = mv->edge_cell_ids[2 * e + 1];
+    if (r < 0) continue;
+    const double dx = mv->cell_xc[r] - mv->cell_xc[l], dy = mv->cell_yc[r] - mv->cell_yc[l];
+    const double d = sqrt(dx * dx + dy * dy), w = d > 0.0 ? 1.0 / d : 0.0;
+    M[3 * l] += w * dx * dx; M[3 * l + 1] += w * dx * dy; M[3 * l + 2] += w * dy * dy;
+    M[3 * r] += w * dx * dx; M[3 * r + 1] += w * dx * dy; M[3 * r + 2] += w * dy * dy;
+  }
+  for (int32_t c = 0; c < nc; ++c) {
+    const double m00 = M[3 * c], m01 = M[3 * c + 1], m11 = M[3 * c + 2], det = m00 * m11 - m01 * m01;
+    if (fabs(det) < 1e-15) continue; /* degenerate: zero gradient */
+    const double id = 1.0 / det;
+    inv[4 * c] = m11 * id; inv[4 * c + 1] = -m01 * id; inv[4 * c + 2] = -m01 * id; inv[4 * c + 3] = m00 * id;
+  }
+  for (int32_t dcell = 0; dcell < L->n_owned; ++dcell) {
+    const int32_t self = L->dev_to_local[dcell];
+    for (int k = 0; k < RDYB_ELL_WIDTH; ++k) {
+      const size_t q = (size_t)k * (size_t)L->stride + (size_t)dcell;
+      if (L->ell_nbr[q] < 0) continue; /* empty or boundary slot: first-order boundary flux, no gradient contribution */
+      const int32_t e = L->ell_edge[q], l = mv->edge_cell_ids[2 * e], r = mv->edge_cell_ids[2 * e + 1];
+      const int32_t other = self == l ? r : l;
+      const double dx = mv->cell_xc[r] - mv->cell_xc[l], dy = mv->cell_yc[r] - mv->cell_yc[l];
+      const double d = sqrt(dx * dx + dy * dy), w = d > 0.0 ? 1.0 / d : 0.0, wdx = w * dx, wdy = w * dy;
+      L->ell_gcx[q] = inv[4 * self] * wdx + inv[4 * self + 1] * wdy;
+      L->ell_gcy[q] = inv[4 * self + 2] * wdx + inv[4 * self + 3] * wdy;
+      L->ell_dxs[q] = mv->edge_xm[e] - mv->cell_xc[self];  L->ell_dys[q] = mv->edge_ym[e] - mv->cell_yc[self];
+      L->ell_dxn[q] = mv->edge_xm[e] - mv->cell_xc[other]; L->ell_dyn[q] = mv->edge_ym[e] - mv->cell_yc[other];
+    }
+  }
+  free(M); free(inv);
+  return RDYB_SUCCESS;
 }
 
 /* ---------------- tiled layout ---------------- */

@@ -43,6 +43,12 @@ typedef struct {
   int32_t *ell_nbr;
   double  *ell_sn, *ell_cn, *ell_slen;
   int32_t *ell_edge;       /* local edge id of the slot (diagnostics) */
+  /* second-order (MUSCL) geometry per ELL slot, built by rdyb_layout_build_muscl (NULL otherwise):
+   *   gcx, gcy : this cell's least-squares gradient weights for the slot's edge, so that grad q += (gcx, gcy) * (q_right - q_left)
+   *              (PrecomputeLSGradCoeffs / ComputeLeastSquaresGradients, src/operator_fluxes_ceed.c:884-1038)
+   *   dxs, dys : edge midpoint - this cell's centroid;  dxn, dyn : edge midpoint - the neighbour's centroid
+   *              (ReconstructFaceValues, src/operator_fluxes_ceed.c:1162-1172) */
+  double *ell_gcx, *ell_gcy, *ell_dxs, *ell_dys, *ell_dxn, *ell_dyn;
   /* flattened boundary-edge table: boundary b owns entries [b_offsets[b], b_offsets[b+1]) in RDyBoundary.edge_ids order */
   int32_t  num_boundaries, num_boundary_edges;
   int32_t *b_offsets;      /* [num_boundaries+1] */
@@ -109,6 +115,7 @@ void rdyb_warp_layout_free(RdybWarpLayout *w);
 
 int  rdyb_layout_build(const RdybMeshView *mesh, int32_t num_boundaries, const RdybBoundaryView *boundaries, const RdybHaloView *halo,
                        int reorder, RdybLayout *out);
+int  rdyb_layout_build_muscl(const RdybMeshView *mesh, RdybLayout *layout);
 void rdyb_layout_free(RdybLayout *layout);
 int  rdyb_tiled_layout_build(const RdybLayout *layout, int32_t tile_cells, RdybTiledLayout *out);
 void rdyb_tiled_layout_free(RdybTiledLayout *tiled);

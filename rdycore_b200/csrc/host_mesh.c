@@ -325,6 +325,7 @@ int rdyb_hostmesh_view(RdybHostMesh m, RdybMeshView *v) {
   v->cell_xc = m->xc; v->cell_yc = m->yc;
   v->edge_cell_ids = m->edge_cells; v->edge_lengths = m->len; v->edge_cn = m->cn; v->edge_sn = m->sn;
   v->internal_edge_ids = m->internal_edge_ids; v->edge_global_ids = m->edge_gid;
+  v->edge_xm = m->exc; v->edge_ym = m->eyc; /* midpoints 0.5*(v0+v1) */
   return RDYB_SUCCESS;
 }
 

@@ -103,6 +103,10 @@ struct RdybOperator_ {
   int32_t ncblocks = 0, ncblocks_interior = 0;
   double *partial = nullptr;
   double *rk_k[4] = {nullptr, nullptr, nullptr, nullptr}, *rk_y = nullptr;
+  /* second order (MUSCL): reconstruction kind (RDYB_RECON_*, 0 = first order), cell gradients [6][stride], per-slot geometry */
+  int recon = 0;
+  double *grad = nullptr, *m_gcx = nullptr, *m_gcy = nullptr, *m_dxs = nullptr, *m_dys = nullptr, *m_dxn = nullptr, *m_dyn = nullptr;
+  bool ghosts_from_caller = false; /* host-Vec apply: u_local arrives with its ghosts filled (DMGlobalToLocal already ran) */
   /* tiled-kernel device arrays */
   TiledDev td;
   bool has_tiled = false;
@@ -171,7 +175,8 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   void *ptrs[] = {op->state[0], op->state[1], op->F, op->src, op->mann, op->fdiv, op->prim, op->inv_area, op->area, op->dzdx, op->dzdy, op->zc,
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
                   op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
-                  op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y};
+                  op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y, op->grad, op->m_gcx, op->m_gcy, op->m_dxs, op->m_dys,
+                  op->m_dxn, op->m_dyn};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (void *p : {(void *)op->pipe.order, (void *)op->pipe.local_to_dev, (void *)op->pipe.owned_to_dev, (void *)op->pipe.stage_in, (void *)op->pipe.stage_out})
@@ -203,6 +208,12 @@ static int operator_create_impl(RdybOperator op, const RdybConfig *config, const
   RDYB_CHECK(config->source_method == RDYB_SOURCE_SEMI_IMPLICIT || config->source_method == RDYB_SOURCE_IMPLICIT_XQ2018, RDYB_ERR_USER,
              "Only semi_implicit and implicit_xq2018 are supported in the PETSc version"); /* src/swe/swe_petsc.c:973-975 */
   RDYB_CHECK(config->well_balancing != RDYB_WELL_BALANCING_HR || mesh->cell_zc, RDYB_ERR_USER, "hydrostatic reconstruction needs cell_zc");
+  RDYB_CHECK(config->reconstruction >= RDYB_RECON_FIRST_ORDER && config->reconstruction <= RDYB_RECON_MUSCL_VANLEER, RDYB_ERR_USER,
+             "Invalid reconstruction: %d", config->reconstruction);
+  /* the HR interior operator has no second-order variant (CreatePetscSWEInteriorFluxHROperator, src/swe/swe_petsc.c:1176-1229) */
+  op->recon = config->well_balancing == RDYB_WELL_BALANCING_HR ? RDYB_RECON_FIRST_ORDER : config->reconstruction;
+  RDYB_CHECK(!op->recon || (mesh->cell_xc && mesh->cell_yc && mesh->edge_xm && mesh->edge_ym), RDYB_ERR_USER,
+             "second-order reconstruction needs cell centroids and edge midpoints in the mesh view");
   for (int32_t b = 0; b < nb; ++b) {
     const int t = bnd[b].bc_type;
     RDYB_CHECK(t == RDYB_CONDITION_DIRICHLET || t == RDYB_CONDITION_REFLECTING || t == RDYB_CONDITION_CRITICAL_OUTFLOW, RDYB_ERR_USER,
@@ -252,6 +263,13 @@ static int operator_create_impl(RdybOperator op, const RdybConfig *config, const
   RDYB_CALL(dalloc(&op->cmax, (size_t)op->ncblocks)); RDYB_CALL(dalloc(&op->carg, (size_t)op->ncblocks));
   CU(cudaMemset(op->carg, 0xff, sizeof(long long) * (size_t)op->ncblocks));
   RDYB_CALL(dalloc(&op->partial, 1024));
+  if (op->recon) {
+    RDYB_CALL(rdyb_layout_build_muscl(mesh, &op->L));
+    RDYB_CALL(dalloc(&op->grad, 6 * S));
+    RDYB_CALL(upload(&op->m_gcx, L.ell_gcx, W)); RDYB_CALL(upload(&op->m_gcy, L.ell_gcy, W));
+    RDYB_CALL(upload(&op->m_dxs, L.ell_dxs, W)); RDYB_CALL(upload(&op->m_dys, L.ell_dys, W));
+    RDYB_CALL(upload(&op->m_dxn, L.ell_dxn, W)); RDYB_CALL(upload(&op->m_dyn, L.ell_dyn, W));
+  }
   return RDYB_SUCCESS;
 }
 
@@ -505,6 +523,7 @@ static void fill_args(RdybOperator op, SweArgs &a, const double *in, double *out
   a.fdiv = op->opt_fdiv ? op->fdiv : nullptr; a.prim = op->opt_prim ? op->prim : nullptr;
   a.cmax = nullptr; a.carg = nullptr;
   a.stride = op->stride; a.width = op->width; a.begin = 0; a.end = 0;
+  a.grad = op->grad; a.gcx = op->m_gcx; a.gcy = op->m_gcy; a.dxs = op->m_dxs; a.dys = op->m_dys; a.dxn = op->m_dxn; a.dyn = op->m_dyn;
   a.dt = dt; a.tiny_h = op->cfg.tiny_h; a.ha2 = op->cfg.h_anuga_regular * op->cfg.h_anuga_regular; a.xq_thr = op->cfg.xq2018_threshold;
 }
 
@@ -513,10 +532,23 @@ static void launch_gather_c(RdybOperator op, const SweArgs &a, int grid) {
   if (op->opt_courant) swe_gather_kernel<HR, SRC, EULER, true><<<grid, RDYB_BLOCK, 0, op->stream>>>(a);
   else swe_gather_kernel<HR, SRC, EULER, false><<<grid, RDYB_BLOCK, 0, op->stream>>>(a);
 }
+template <int SRC, bool EULER, int RECON>
+static void launch_gather_r(RdybOperator op, const SweArgs &a, int grid) {
+  if (op->opt_courant) swe_gather_kernel<false, SRC, EULER, true, RECON><<<grid, RDYB_BLOCK, 0, op->stream>>>(a);
+  else swe_gather_kernel<false, SRC, EULER, false, RECON><<<grid, RDYB_BLOCK, 0, op->stream>>>(a);
+}
 template <bool EULER>
 static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
   const bool hr = op->cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = op->cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
+  if (op->recon) { /* second order (never HR) */
+    switch (op->recon) {
+      case RDYB_RECON_MUSCL_MINMOD: if (xq) launch_gather_r<1, EULER, RDYB_RECON_MUSCL_MINMOD>(op, a, grid); else launch_gather_r<0, EULER, RDYB_RECON_MUSCL_MINMOD>(op, a, grid); break;
+      case RDYB_RECON_MUSCL_NONE: if (xq) launch_gather_r<1, EULER, RDYB_RECON_MUSCL_NONE>(op, a, grid); else launch_gather_r<0, EULER, RDYB_RECON_MUSCL_NONE>(op, a, grid); break;
+      default: if (xq) launch_gather_r<1, EULER, RDYB_RECON_MUSCL_VANLEER>(op, a, grid); else launch_gather_r<0, EULER, RDYB_RECON_MUSCL_VANLEER>(op, a, grid); break;
+    }
+    return;
+  }
   if (hr) { if (xq) launch_gather_c<true, 1, EULER>(op, a, grid); else launch_gather_c<true, 0, EULER>(op, a, grid); }
   else { if (xq) launch_gather_c<false, 1, EULER>(op, a, grid); else launch_gather_c<false, 0, EULER>(op, a, grid); }
 }
@@ -524,7 +556,7 @@ static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
 /* one RHS / Euler pass over owned device cells [begin,end) */
 static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
   if (end <= begin) return RDYB_SUCCESS;
-  if (op->kernel_kind >= 1 && op->has_tiled) {
+  if (op->kernel_kind >= 1 && op->has_tiled && !op->recon) { /* the second-order path runs on K1 */
     /* interior tiles and frontier tiles (thin strips along the partition border, with many more outside neighbours) are
      * launched separately so that each part can use the most specialised kernel its tiles fit */
     if (begin < op->NI && end > op->NI) {
@@ -557,7 +589,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
   fill_args(op, a, in, out, dt);
   a.begin = begin; a.end = end;
   if (op->opt_courant) { a.cmax = op->cmax + cslot0; a.carg = op->carg + cslot0; }
-  op->last_kernel = "swe_gather_kernel (K1)";
+  op->last_kernel = op->recon ? "swe_gather_kernel (K1, MUSCL) + muscl_gradient_kernel" : "swe_gather_kernel (K1)";
   const int grid = grid_for(end - begin, RDYB_BLOCK);
   if (euler) launch_gather<true>(op, a, grid);
   else launch_gather<false>(op, a, grid);
@@ -714,7 +746,24 @@ static int p2p_wait(RdybOperator op) {
 
 /* one RHS (or fused Euler) evaluation of `in` into `out`, with the halo exchange of `in` overlapped with the interior cells */
 static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool euler) {
-  const bool exchange = op->L.num_peers > 0 && op->comm;
+  const bool exchange = op->L.num_peers > 0 && op->comm && !op->ghosts_from_caller;
+  if (op->recon) {
+    /* second order: state halo, gradients of the owned cells, gradient halo (two [3][stride] blocks: d/dx and d/dy, the two
+     * passes of CommunicateCellGradients), then the reconstructed fluxes.  No overlap yet: this row is correctness-first. */
+    RDYB_CHECK(op->L.num_peers == 0 || op->comm, RDYB_ERR_USER,
+               "second order on a partitioned mesh exchanges cell gradients: call rdyb_operator_init_comm first");
+    if (exchange) { RDYB_CALL(halo_begin(op, in)); RDYB_CALL(halo_end(op)); }
+    SweArgs g;
+    fill_args(op, g, in, out, dt);
+    muscl_gradient_kernel<<<grid_for(op->N, 128), 128, 0, op->stream>>>(g, op->grad, op->N);
+    LAUNCHED();
+    CU(cudaGetLastError());
+    if (op->L.num_peers > 0) {
+      RDYB_CALL(halo_begin(op, op->grad)); RDYB_CALL(halo_end(op));
+      RDYB_CALL(halo_begin(op, op->grad + 3 * (size_t)op->stride)); RDYB_CALL(halo_end(op));
+    }
+    return launch_cells(op, in, out, dt, euler, 0, op->N, 0);
+  }
   if (exchange) {
     RDYB_CALL(halo_begin(op, in));
     RDYB_CALL(launch_cells(op, in, out, dt, euler, 0, op->NI, 0));
@@ -843,7 +892,7 @@ static int apply_host_pipelined(RdybOperator op, double dt, const double *u_loca
 extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double *u_local, double *f_global) {
   RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
-  if (op->kernel_kind >= 2 && op->kernel_kind <= 3 && op->has_tiled) { /* K3 / K4: chunked, overlapped copies */
+  if (op->kernel_kind >= 2 && op->kernel_kind <= 3 && op->has_tiled && !op->recon) { /* K3 / K4: chunked, overlapped copies */
     if (!op->pipe.built || op->pipe.tile_cells != op->T.tile_cells) RDYB_CALL(pipe_build(op));
     if (op->pipe.usable) return apply_host_pipelined(op, dt, u_local, f_global);
   }
@@ -852,11 +901,10 @@ extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double
   aos_to_soa_kernel<<<grid_for(op->NL, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_local, op->state[op->cur], op->NL, op->stride);
   LAUNCHED();
   CU(cudaGetLastError());
-  /* ghosts come from the caller here (DMGlobalToLocal already ran): no exchange */
-  ncclComm_t saved = op->comm;
-  op->comm = nullptr;
+  /* ghosts come from the caller here (DMGlobalToLocal already ran): no state exchange */
+  op->ghosts_from_caller = true;
   int ierr = rhs_pass(op, op->state[op->cur], op->F, dt, false);
-  op->comm = saved;
+  op->ghosts_from_caller = false;
   RDYB_CALL(ierr);
   soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->F, op->dev_to_owned, op->stage, op->N, op->stride);
   LAUNCHED();
@@ -885,7 +933,7 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
   RDYB_CHECK(nsteps >= 0, RDYB_ERR_ARG, "negative step count");
   CU(cudaSetDevice(op->device));
   CU(cudaEventRecord(op->ev_t0, op->stream));
-  if (op->p2p && nsteps > 0) {
+  if (op->p2p && nsteps > 0 && !op->recon) {
     /* peer-memory halo: the two state buffers alternate, so a neighbour's push for step s+1 lands in the buffer this rank
      * does not read during step s, and its counter (raised after its frontier kernel) orders everything else */
     RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));

@@ -42,7 +42,44 @@ struct SweArgs {
   long long *__restrict__ carg;
   int32_t stride, width, begin, end;
   double dt, tiny_h, ha2, xq_thr;
+  /* second order (MUSCL, K1 only): cell gradients SoA [6][stride] = d/dx (h,hu,hv), d/dy (h,hu,hv) incl. ghost cells, and the
+   * per-slot least-squares weights / face offsets of device_layout.h; all NULL for first order */
+  const double *__restrict__ grad;
+  const double *__restrict__ gcx, *__restrict__ gcy, *__restrict__ dxs, *__restrict__ dys, *__restrict__ dxn, *__restrict__ dyn;
 };
+
+/* slope limiters of the MUSCL reconstruction, src/operator_fluxes_ceed.c:1100-1132: the extrapolated increment is limited
+ * against half the cell-to-cell jump */
+template <int RECON>
+__device__ __forceinline__ double swe_limit_slope(double extrap, double half_dq) {
+  if (RECON == RDYB_RECON_MUSCL_NONE) return extrap;
+  if (extrap * half_dq <= 0.0) return 0.0;
+  if (RECON == RDYB_RECON_MUSCL_VANLEER) return 2.0 * extrap * half_dq / (extrap + half_dq);
+  return fabs(extrap) < fabs(half_dq) ? extrap : half_dq; /* minmod */
+}
+
+/* ComputeLeastSquaresGradients, src/operator_fluxes_ceed.c:993-1038, turned cell-centric: one thread per owned cell sums
+ * weight * (q_right - q_left) over its interior edges in the reference's edge order (no atomics).  Ghost-cell gradients arrive
+ * by halo exchange (CommunicateCellGradients, :1056-1098). */
+__global__ void muscl_gradient_kernel(const SweArgs a, double *__restrict__ grad, int32_t n_owned) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_owned) return;
+  const double q0 = a.h[i], q1 = a.hu[i], q2 = a.hv[i];
+  double gx0 = 0.0, gx1 = 0.0, gx2 = 0.0, gy0 = 0.0, gy1 = 0.0, gy2 = 0.0;
+#pragma unroll
+  for (int k = 0; k < RDYB_ELL_WIDTH; ++k) {
+    if (k >= a.width) break;
+    const size_t q = (size_t)k * (size_t)a.stride + (size_t)i;
+    const int nbr = a.nbr[q];
+    if (nbr < 0) continue; /* empty or boundary slot */
+    const double sgn = a.eslen[q] < 0.0 ? 1.0 : -1.0; /* left cell: q_nbr - q_self; right cell: q_self - q_nbr */
+    const double d0 = sgn * (a.h[nbr] - q0), d1 = sgn * (a.hu[nbr] - q1), d2 = sgn * (a.hv[nbr] - q2);
+    const double cx = a.gcx[q], cy = a.gcy[q];
+    gx0 += cx * d0; gy0 += cy * d0; gx1 += cx * d1; gy1 += cy * d1; gx2 += cx * d2; gy2 += cy * d2;
+  }
+  const size_t S = (size_t)a.stride;
+  grad[i] = gx0; grad[S + i] = gx1; grad[2 * S + i] = gx2; grad[3 * S + i] = gy0; grad[4 * S + i] = gy1; grad[5 * S + i] = gy2;
+}
 
 __device__ __forceinline__ void courant_block_reduce(double cmax, long long carg, double *slot_val, long long *slot_arg) {
   /* max over the block; ties go to the smaller arg so the result does not depend on scheduling */
@@ -64,7 +101,7 @@ __device__ __forceinline__ void courant_block_reduce(double cmax, long long carg
   }
 }
 
-template <bool HR, int SRC, bool EULER, bool COURANT>
+template <bool HR, int SRC, bool EULER, bool COURANT, int RECON = 0>
 __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a) {
   const int i = a.begin + blockIdx.x * RDYB_BLOCK + threadIdx.x;
   double cmax = 0.0;
@@ -87,7 +124,38 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
       if (nbr == RDYB_NO_EDGE) continue;
       const double sn = a.esn[q], cn = a.ecn[q], slen = a.eslen[q];
       const double scale = slen * ia; /* -L/A when this cell is the left cell, +L/A when it is the right cell */
-      if (nbr >= 0) {
+      if (RECON != 0 && nbr >= 0) {
+        /* second order: ReconstructFaceValues (src/operator_fluxes_ceed.c:1150-1195) + ApplyInteriorFlux2R (src/swe/swe_petsc.c:140-200) */
+        const bool left = slen < 0.0;
+        const size_t S = (size_t)a.stride;
+        const int cl = left ? i : nbr, cr = left ? nbr : i;
+        const double dxl = left ? a.dxs[q] : a.dxn[q], dyl = left ? a.dys[q] : a.dyn[q];
+        const double dxr = left ? a.dxn[q] : a.dxs[q], dyr = left ? a.dyn[q] : a.dys[q];
+        double fl[3], fr[3];
+        const double *qv[3] = {a.h, a.hu, a.hv};
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const double ql = qv[c][cl], qr = qv[c][cr];
+          const double el = a.grad[c * S + cl] * dxl + a.grad[(3 + c) * S + cl] * dyl;
+          const double er = a.grad[c * S + cr] * dxr + a.grad[(3 + c) * S + cr] * dyr;
+          const double dq = qr - ql;
+          fl[c] = ql + swe_limit_slope<RECON>(el, 0.5 * dq);
+          fr[c] = qr + swe_limit_slope<RECON>(er, -0.5 * dq);
+        }
+        const double hl = fmax(0.0, fl[0]), hr = fmax(0.0, fr[0]);
+        if (hl < tiny && hr < tiny) continue; /* src/swe/swe_petsc.c:179 */
+        double ul, vl, ur, vr;
+        swe_velocities<false>(hl, fl[1], fl[2], tiny, a.ha2, ul, vl);
+        swe_velocities<false>(hr, fr[1], fr[2], tiny, a.ha2, ur, vr);
+        const RoeFlux f = swe_roe_flux(hl, ul, vl, swe_sqrt(hl), hr, ur, vr, swe_sqrt(hr), sn, cn);
+        if (COURANT) {
+          const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * a.dt;
+          if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
+        }
+        F0 += f.f0 * scale;
+        F1 += f.f1 * scale;
+        F2 += f.f2 * scale;
+      } else if (nbr >= 0) {
         const double hn = a.h[nbr];
         if (hn < tiny && h < tiny) continue; /* src/swe/swe_petsc.c:285, :1096 */
         const double hun = a.hu[nbr], hvn = a.hv[nbr];
