@@ -213,6 +213,17 @@ static int read_config(RDy rdy) {
     RDYB_CHECK(!t || strcmp(t, "beuler"), RDYB_ERR_SUP, "numerics.temporal: beuler (implicit, SNES) is outside the explicit B200 path");
     RDYB_CALL(deck_enum(entries, n, "numerics.temporal", tn, tv, 2, &v));
     rdy->physics.temporal = v;
+    /* numerics.second_order / limiter / no_limiter (src/yaml_input.c:130-143; resolved as src/swe/swe_petsc.c:357-369) */
+    static const char *const bn[] = {"true", "false"};
+    static const int bv[] = {1, 0};
+    int second = 0, nolim = 0, lim = 0;
+    RDYB_CALL(deck_enum(entries, n, "numerics.second_order", bn, bv, 2, &second));
+    RDYB_CALL(deck_enum(entries, n, "numerics.no_limiter", bn, bv, 2, &nolim));
+    static const char *const ln[] = {"minmod", "none", "van_leer"};
+    static const int lv[] = {0, 1, 2};
+    RDYB_CALL(deck_enum(entries, n, "numerics.limiter", ln, lv, 3, &lim));
+    if (nolim) lim = 1;
+    rdy->physics.reconstruction = !second ? RDYB_RECON_FIRST_ORDER : lim == 1 ? RDYB_RECON_MUSCL_NONE : lim == 2 ? RDYB_RECON_MUSCL_VANLEER : RDYB_RECON_MUSCL_MINMOD;
     static const char *const rn[] = {"roe"};
     static const int rv[] = {0};
     RDYB_CALL(deck_enum(entries, n, "numerics.riemann", rn, rv, 1, &v));

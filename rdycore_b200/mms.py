@@ -91,3 +91,5 @@ def convergence_rates(num_cells, norms) -> np.ndarray:
 
 # mms.convergence.expected_rates of mms_conv_study.yaml:49-64 (a rate must EXCEED its threshold, src/rdymms.c:1005-1008)
 EXPECTED_RATES = {"h": (0.94, 0.95, 0.94), "hu": (0.91, 0.93, 0.77), "hv": (0.91, 0.93, 0.77)}
+# driver/tests/swe_roe/mms_conv_study_second_order.yaml:57-69
+EXPECTED_RATES_SECOND_ORDER = {"h": (1.40, 1.20, 0.80), "hu": (1.30, 1.30, 0.85), "hv": (1.30, 1.30, 0.85)}

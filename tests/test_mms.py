@@ -22,7 +22,7 @@ FORMS = mms.Forms()
 DT, NSTEPS = 0.01, 500  # time.time_step, time.stop / time_step
 
 
-def mms_case(level: int) -> cases.Case:
+def mms_case(level: int, reconstruction=cases.FIRST_ORDER) -> cases.Case:
     fx = np.load(os.path.join(HERE, "golden", "mms_triangles_dx1.npz"))
     cells = fx["cells"]
     mesh = HostMesh.from_cells(fx["xyz"], np.arange(0, 3 * len(cells) + 1, 3, dtype=np.int32), cells.ravel())
@@ -34,7 +34,7 @@ def mms_case(level: int) -> cases.Case:
     n = mesh.num_owned_cells
     x, y = mesh.array("cell_xc")[:n], mesh.array("cell_yc")[:n]
     u0 = FORMS.solution(x, y, 0.0)
-    case = cases.Case(f"mms_level{level}", mesh, cases.make_config(), bnd, u0, FORMS.mannings(x, y), np.zeros((n, 3)), DT)
+    case = cases.Case(f"mms_level{level}", mesh, cases.make_config(reconstruction=reconstruction), bnd, u0, FORMS.mannings(x, y), np.zeros((n, 3)), DT)
     be = bnd[0].edge_ids
     case.info.update(x=x, y=y, xe=mesh.array("edge_xc")[be], ye=mesh.array("edge_yc")[be], areas=mesh.view_arrays()["cell_areas"][:n].copy())
     return case
@@ -53,7 +53,8 @@ def run_oracle(case, nsteps=NSTEPS):
 
 def run_gpu(case, nsteps=NSTEPS):
     rdy.RDyInit()
-    r = rdy.RDy(os.path.join(HERE, "decks", "mms.yaml"))
+    deck = "mms_second_order.yaml" if case.config.reconstruction else "mms.yaml"
+    r = rdy.RDy(os.path.join(HERE, "decks", deck))
     arr, nb = case.boundary_views()
     r.set_mesh(case.mesh, arr, nb)
     r.RDySetup()
@@ -127,3 +128,41 @@ def test_cuda_path_meets_the_reference_convergence_thresholds():
         for k in range(3):
             rate = mms.convergence_rates(ncells, [[n[k][c]] for n in norms])[0]
             assert rate > mms.EXPECTED_RATES[name][k]
+
+
+# ---- second order: driver/tests/swe_roe/mms_conv_study_second_order.yaml (numerics.second_order: true, minmod) ----
+def _rates(run, reconstruction):
+    ncells, norms = [], []
+    for lv in [1, 2, 3, 4]:
+        case = mms_case(lv, reconstruction)
+        u = run(case)
+        i = case.info
+        norms.append(mms.error_norms(u, FORMS.solution(i["x"], i["y"], NSTEPS * DT), i["areas"]))
+        ncells.append(case.mesh.num_owned_cells)
+    return {name: [float(mms.convergence_rates(ncells, [[n[k][c]] for n in norms])[0]) for k in range(3)] for c, name in enumerate(("h", "hu", "hv"))}
+
+
+def test_oracle_meets_the_second_order_thresholds():
+    """The pin of the restated MUSCL helpers (oracle/muscl_helpers.h): the reference's CI thresholds for its second-order run."""
+    rates = _rates(run_oracle, cases.MUSCL_MINMOD)
+    for name, got in rates.items():
+        for k in range(3):
+            assert got[k] > mms.EXPECTED_RATES_SECOND_ORDER[name][k], f"{name} norm {k}: rate {got[k]}"
+    assert rates["h"][0] > 1.4  # clearly better than the first-order run (~1.0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("level", [1, 2])
+def test_cuda_second_order_matches_the_oracle_on_the_mms_problem(level):
+    case = mms_case(level, cases.MUSCL_MINMOD)
+    u_ref = run_oracle(case)
+    u = run_gpu(case)
+    assert_state_close(u, u_ref, what=f"second-order MMS level {level}")
+
+
+@pytest.mark.gpu
+def test_cuda_second_order_meets_the_reference_thresholds():
+    rates = _rates(run_gpu, cases.MUSCL_MINMOD)
+    for name, got in rates.items():
+        for k in range(3):
+            assert got[k] > mms.EXPECTED_RATES_SECOND_ORDER[name][k]
