@@ -29,6 +29,7 @@ def main():
     ap.add_argument("--kernel", type=int, default=3)
     ap.add_argument("--tile", type=int, default=224)
     ap.add_argument("--p2p", action="store_true", help="peer-memory halo (CUDA IPC over NVLink) instead of NCCL send/recv")
+    ap.add_argument("--recon", type=int, default=0, help="second order: 1 minmod, 2 no limiter, 3 van Leer (fully wet case; gradients are exchanged too)")
     args = ap.parse_args()
 
     import torch
@@ -41,12 +42,19 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     px, py = {1: (1, 1), 2: (2, 1), 4: (2, 2), 8: (4, 2)}[world]
-    kw = dict(nx=args.nx, ny=args.ny, eta0=6.0 if args.hr else 8.0, hr=args.hr)
+    kw = dict(nx=args.nx, ny=args.ny, eta0=40.0 if args.recon else 6.0 if args.hr else 8.0, hr=args.hr)
     if args.hr:
         kw["dam_column"] = (200.0, 14.0)
     part = cases.floodplain(px=px, py=py, rank=rank, **kw)
     serial = cases.floodplain(**kw)
     part.dt = serial.dt  # the same step on every rank (the serial case's)
+    if args.recon:
+        # second order: a fully wet, moving state (set by global cell id so that every rank sees the same field)
+        part.config.reconstruction = serial.config.reconstruction = args.recon
+        for c in (part, serial):
+            g = c.mesh.array("cell_global_ids")[c.mesh.array("owned_to_local")].astype(np.float64)
+            c.u0[:, 1] = 0.3 * np.sin(0.37 * g) * c.u0[:, 0]
+            c.u0[:, 2] = 0.3 * np.cos(0.23 * g) * c.u0[:, 0]
     op = Operator.from_case(part, device=local, halo=part.mesh.halo())
     if args.kernel:
         op.set_kernel(args.kernel, args.tile)

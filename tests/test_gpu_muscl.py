@@ -31,13 +31,17 @@ def test_dam_break_quads_second_order(reconstruction, source_method):
     oracle = make_oracle(case)
     op = Operator.from_case(case)
     op.set_kernel(TILED_FIXED, 224)  # a tiled kernel may be selected: the second-order path still runs (on K1)
-    op.step_euler(case.dt, 400)
-    oracle.step_euler(case.dt, 400)
+    # Van Leer's smooth limiter amplifies round-off faster than minmod: the CPU port compiled with and without FMA contraction
+    # (scratch/fma/sens.py, same C source) differs by 4e-12 / 9e-12 / 1.7e-11 after 100 / 200 / 400 steps on this case, the
+    # GPU by 1.15e-11 after 400 — so the 1e-11 tolerance is checked at 150 steps there, 400 for minmod and unlimited.
+    steps = 150 if reconstruction == cases.MUSCL_VANLEER else 400
+    op.step_euler(case.dt, steps)
+    oracle.step_euler(case.dt, steps)
     assert "MUSCL" in op.kernel_info()
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order dam break")
     first = cases.dam_break_quads(nx=60, ny=60, source_method=source_method)
     o1 = make_oracle(first)
-    o1.step_euler(case.dt, 400)
+    o1.step_euler(case.dt, steps)
     assert np.abs(o1.array("u_global") - oracle.array("u_global")).max() > 1e-2  # it really is a different scheme
 
 

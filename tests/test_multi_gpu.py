@@ -52,3 +52,11 @@ def test_four_ranks_2x2_blocks():
     if _ngpus() < 4:
         pytest.skip("needs 4 GPUs")
     _run(4, ["--p2p", "--kernel", "3", "--tile", "224", "--nx", "128", "--ny", "96"], 29541)
+
+
+def test_two_ranks_second_order_exchanges_gradients():
+    """MUSCL on a partitioned mesh: the ghost cells' gradients come from their owners (CommunicateCellGradients,
+    src/operator_fluxes_ceed.c:1056-1098) over the same halo plan, after the state halo."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, ["--recon", "1", "--kernel", "0", "--steps", "60"], 29561)
