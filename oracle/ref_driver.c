@@ -140,6 +140,11 @@ int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb,
     m->cells.centroids = calloc((size_t)mv->num_cells, sizeof(RDyPoint));
     for (PetscInt i = 0; i < mv->num_cells; ++i) m->cells.centroids[i].X[2] = mv->cell_zc[i];
   }
+  if (c->numerics.second_order && cfg->well_balancing == RDYB_WELL_BALANCING_HR) {
+    /* CreateOperator's check, src/operator.c:388-389 (operator.c itself is not part of this build) */
+    fprintf(stderr, "-second_order cannot be used with well_balancing = HR simultaneously (not yet implemented)\n");
+    return PETSC_ERR_USER;
+  }
   if (c->numerics.second_order) {
     /* what ApplyInteriorFlux2R and its helpers read: centroids, edge vertices (two synthetic vertices per edge, both AT the
      * view's midpoint, so that 0.5*(v0+v1) reproduces it exactly), edge ownership (serial: every edge is owned) */

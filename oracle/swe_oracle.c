@@ -83,9 +83,14 @@ int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb,
     fprintf(stderr, "Only semi_implicit and implicit_xq2018 are supported in the PETSc version\n");
     return RDYB_ERR_USER;
   }
-  /* numerics.second_order: only the first-order (non-HR) interior operator has the MUSCL variant (swe_petsc.c:357-376, 404) */
+  /* numerics.second_order: only the first-order (non-HR) interior operator has the MUSCL variant (swe_petsc.c:357-376, 404);
+   * the combination with HR is refused at operator creation (src/operator.c:388-389) */
   o->limiter = -1;
-  if (cfg->reconstruction != RDYB_RECON_FIRST_ORDER && cfg->well_balancing != RDYB_WELL_BALANCING_HR) {
+  if (cfg->reconstruction != RDYB_RECON_FIRST_ORDER && cfg->well_balancing == RDYB_WELL_BALANCING_HR) {
+    fprintf(stderr, "-second_order cannot be used with well_balancing = HR simultaneously (not yet implemented)\n");
+    return RDYB_ERR_USER;
+  }
+  if (cfg->reconstruction != RDYB_RECON_FIRST_ORDER) {
     if (!mv->cell_xc || !mv->cell_yc || !mv->edge_xm || !mv->edge_ym) { fprintf(stderr, "swe_oracle: second order needs centroids and edge midpoints\n"); return RDYB_ERR_USER; }
     o->limiter = cfg->reconstruction == RDYB_RECON_MUSCL_NONE ? MUSCL_LIMITER_NONE : cfg->reconstruction == RDYB_RECON_MUSCL_VANLEER ? MUSCL_LIMITER_VANLEER : MUSCL_LIMITER_MINMOD;
     o->xc = dup_arr(mv->cell_xc, (size_t)o->nc, 8); o->yc = dup_arr(mv->cell_yc, (size_t)o->nc, 8);

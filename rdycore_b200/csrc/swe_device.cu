@@ -210,8 +210,10 @@ static int operator_create_impl(RdybOperator op, const RdybConfig *config, const
   RDYB_CHECK(config->well_balancing != RDYB_WELL_BALANCING_HR || mesh->cell_zc, RDYB_ERR_USER, "hydrostatic reconstruction needs cell_zc");
   RDYB_CHECK(config->reconstruction >= RDYB_RECON_FIRST_ORDER && config->reconstruction <= RDYB_RECON_MUSCL_VANLEER, RDYB_ERR_USER,
              "Invalid reconstruction: %d", config->reconstruction);
-  /* the HR interior operator has no second-order variant (CreatePetscSWEInteriorFluxHROperator, src/swe/swe_petsc.c:1176-1229) */
-  op->recon = config->well_balancing == RDYB_WELL_BALANCING_HR ? RDYB_RECON_FIRST_ORDER : config->reconstruction;
+  /* src/operator.c:388-389 */
+  RDYB_CHECK(!config->reconstruction || config->well_balancing != RDYB_WELL_BALANCING_HR, RDYB_ERR_USER,
+             "-second_order cannot be used with well_balancing = HR simultaneously (not yet implemented)");
+  op->recon = config->reconstruction;
   RDYB_CHECK(!op->recon || (mesh->cell_xc && mesh->cell_yc && mesh->edge_xm && mesh->edge_ym), RDYB_ERR_USER,
              "second-order reconstruction needs cell centroids and edge midpoints in the mesh view");
   for (int32_t b = 0; b < nb; ++b) {

@@ -50,8 +50,13 @@ def test_wet_triangle_floodplain_second_order(reconstruction):
     case = _wet_floodplain(reconstruction)
     oracle = make_oracle(case)
     op = Operator.from_case(case)
-    op.step_euler(case.dt, 200)
-    oracle.step_euler(case.dt, 200)
+    if reconstruction == cases.MUSCL_VANLEER:
+        # van Leer + forward Euler is unstable on this rough state (the oracle itself reaches NaN by step 200): RK4 there
+        op.step_rk4(case.dt, 100)
+        oracle.step_rk4(case.dt, 100)
+    else:
+        op.step_euler(case.dt, 200)
+        oracle.step_euler(case.dt, 200)
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order floodplain")
 
 
@@ -78,15 +83,11 @@ def test_second_order_rhs_courant_and_rk4():
     assert np.array_equal(op2.get_state(), op.get_state())
 
 
-def test_hr_ignores_second_order_like_the_reference():
-    """CreatePetscSWEInteriorFluxHROperator has no MUSCL variant (src/swe/swe_petsc.c:1176-1229): HR + second_order runs HR."""
-    a = cases.floodplain(nx=32, ny=28, eta0=9.0, hr=True)
-    b = cases.floodplain(nx=32, ny=28, eta0=9.0, hr=True)
-    b.config.reconstruction = cases.MUSCL_MINMOD
-    oa, ob = Operator.from_case(a), Operator.from_case(b)
-    oa.step_euler(a.dt, 50)
-    ob.step_euler(a.dt, 50)
-    assert np.array_equal(oa.get_state(), ob.get_state())
-    oracle = make_oracle(b)
-    oracle.step_euler(a.dt, 50)
-    assert_state_close(ob.get_state(), oracle.array("u_global"), what="HR with second_order set")
+def test_hr_with_second_order_is_refused_like_the_reference():
+    """CreateOperator: "-second_order cannot be used with well_balancing = HR simultaneously" (src/operator.c:388-389)."""
+    case = cases.floodplain(nx=32, ny=28, eta0=9.0, hr=True)
+    case.config.reconstruction = cases.MUSCL_MINMOD
+    with pytest.raises(RuntimeError, match="second_order cannot be used with well_balancing = HR"):
+        Operator.from_case(case)
+    with pytest.raises(RuntimeError):
+        make_oracle(case)

@@ -154,10 +154,18 @@ def test_oracle_meets_the_second_order_thresholds():
 @pytest.mark.gpu
 @pytest.mark.parametrize("level", [1, 2])
 def test_cuda_second_order_matches_the_oracle_on_the_mms_problem(level):
+    """States after 100 steps at the 1e-11 tolerance; after the full 500 the error norms only.  MUSCL + forward Euler amplifies
+    round-off: the CPU port compiled with and without FMA contraction (scratch/fma/sens3.py, same C source) differs by 3e-12
+    after 100 steps and 1.9e-11 after 500 on level 2 (1.7e-10 on level 3); the GPU differs from the oracle by 2.3e-11 at 500."""
     case = mms_case(level, cases.MUSCL_MINMOD)
+    assert_state_close(run_gpu(case, 100), run_oracle(case, 100), what=f"second-order MMS level {level}, 100 steps")
     u_ref = run_oracle(case)
     u = run_gpu(case)
-    assert_state_close(u, u_ref, what=f"second-order MMS level {level}")
+    assert_state_close(u, u_ref, rel=1e-9, what=f"second-order MMS level {level}")
+    i = case.info
+    exact = FORMS.solution(i["x"], i["y"], NSTEPS * DT)
+    for a, b in zip(mms.error_norms(u, exact, i["areas"]), mms.error_norms(u_ref, exact, i["areas"])):
+        assert np.allclose(a, b, rtol=1e-8, atol=0.0)
 
 
 @pytest.mark.gpu
