@@ -39,7 +39,7 @@ def parse_args():
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--nx", type=int, default=2236, help="quads per side of one GPU's block (cells = 2*nx*ny)")
     p.add_argument("--ny", type=int, default=0)
-    p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed", "warp"])
+    p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed", "warp", "split"])
     p.add_argument("--tile", type=int, default=int(os.environ.get("RDYB_TILE", "224")))
     p.add_argument("--no-courant", action="store_true", help="skip the per-edge Courant diagnostic (the reference always computes it)")
     p.add_argument("--e2e-steps", type=int, default=10)
@@ -213,7 +213,7 @@ def run_b200_arm(args):
 
     from rdycore_b200 import cases
     from rdycore_b200._lib import lib
-    from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, Operator, kernel_launch_count
+    from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP, Operator, kernel_launch_count
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -237,8 +237,8 @@ def run_b200_arm(args):
         case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=18.0 if args.eta0 is None else args.eta0, px=px, py=py, rank=rank)
     halo = case.mesh.halo() if world > 1 else None
     op = Operator.from_case(case, device=local_rank, halo=halo)
-    kernel = {"auto": TILED_FIXED, "gather": GATHER, "tiled": TILED, "async": TILED_ASYNC, "fixed": TILED_FIXED, "warp": WARP}[args.kernel]
-    kernel_name = {GATHER: "gather", TILED: "tiled", TILED_ASYNC: "tiled_async", TILED_FIXED: "tiled_fixed", WARP: "warp"}[kernel]
+    kernel = {"auto": TILED_FIXED, "gather": GATHER, "tiled": TILED, "async": TILED_ASYNC, "fixed": TILED_FIXED, "warp": WARP, "split": TILED_SPLIT}[args.kernel]
+    kernel_name = {GATHER: "gather", TILED: "tiled", TILED_ASYNC: "tiled_async", TILED_FIXED: "tiled_fixed", WARP: "warp", TILED_SPLIT: "tiled_split"}[kernel]
     op.set_kernel(kernel, args.tile)
     op.set_options(courant=not args.no_courant)
     if world > 1:

@@ -22,6 +22,7 @@
 #include "swe_tiled.cuh"
 #include "swe_tiled_async.cuh"
 #include "swe_tiled_fixed.cuh"
+#include "swe_tiled_split.cuh"
 #include "swe_warp.cuh"
 
 static std::atomic<int64_t> g_launches{0};
@@ -116,7 +117,8 @@ struct RdybOperator_ {
   const char *last_kernel = "none";
   bool has_warp = false, warp_used = false; /* warp_used: the last launch ran K5 (not a fallback) */
   int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3),
-                          4 = one 32-cell mini-tile per warp (K5; falls back to K4 / K3) */
+                          4 = one 32-cell mini-tile per warp (K5; falls back to K4 / K3), 5 = K4's pipeline with the work split across
+                          threads and no producer warp (K6; falls back to K4 / K3) */
   /* options */
   bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
   bool mom_src = false; /* any momentum external source set */
@@ -321,7 +323,7 @@ static void pipe_release(RdybOperator op);
 /* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
-  RDYB_CHECK(kind >= 0 && kind <= 4, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
+  RDYB_CHECK(kind >= 0 && kind <= 5, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
   CU(cudaSetDevice(op->device));
   if (kind >= 1) {
     if (op->has_tiled && op->T.tile_cells != tile_cells) {
@@ -573,7 +575,10 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     const int mh = interior ? op->T.max_halo_interior : op->T.max_halo, me = interior ? op->T.max_edges_interior : op->T.max_edges;
     op->warp_used = op->kernel_kind == 4 && op->has_warp && warp_applicable(op->WL, t);
     if (op->warp_used) { op->last_kernel = "swe_warp_kernel (K5)"; RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream)); }
-    else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T.tile_cells, mh, me, t)) {
+    else if (op->kernel_kind == 5 && tiled_split_applicable(op->td, op->T.tile_cells, mh, me, t)) {
+      if (interior || op->NI == 0) op->last_kernel = "swe_tiled_split_kernel (K6)";
+      RDYB_CALL(tiled_split_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
+    } else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T.tile_cells, mh, me, t)) {
       if (interior || op->NI == 0) op->last_kernel = "swe_tiled_fixed_kernel (K4)";
       RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, mh, me, op->stream));
     } else if (op->kernel_kind >= 2) {
@@ -894,7 +899,7 @@ static int apply_host_pipelined(RdybOperator op, double dt, const double *u_loca
 extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double *u_local, double *f_global) {
   RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
-  if (op->kernel_kind >= 2 && op->kernel_kind <= 3 && op->has_tiled && !op->recon) { /* K3 / K4: chunked, overlapped copies */
+  if ((op->kernel_kind == 2 || op->kernel_kind == 3 || op->kernel_kind == 5) && op->has_tiled && !op->recon) { /* K3 / K4: chunked, overlapped copies */
     if (!op->pipe.built || op->pipe.tile_cells != op->T.tile_cells) RDYB_CALL(pipe_build(op));
     if (op->pipe.usable) return apply_host_pipelined(op, dt, u_local, f_global);
   }

@@ -9,7 +9,7 @@ import pytest
 
 from rdycore_b200 import cases
 from rdycore_b200.mesh import HostMesh
-from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, Operator
+from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP, Operator
 
 from util import REL_TOL, assert_state_close, make_oracle, state_error
 
@@ -17,7 +17,8 @@ pytestmark = pytest.mark.gpu
 
 WARP128 = (WARP, 128)  # K5 with 128-cell staged tiles and a 4-deep pipeline
 FIXED224 = (TILED_FIXED, 224)  # K4 shape with 7 consumer warps and three CTAs per SM (the bench default)
-KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, FIXED224, WARP, WARP128]
+SPLIT224 = (TILED_SPLIT, 224)  # K6: K4's pipeline, work split across 384 threads, no producer warp
+KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, FIXED224, SPLIT224, WARP, WARP128]
 
 
 def _op(case, kernel=GATHER, **opts):
@@ -67,6 +68,10 @@ def test_floodplain_triangles_semi_implicit(kernel, rain):
         op.step_euler(case.dt, 100)
         oracle.step_euler(case.dt, 100)
         assert_state_close(op.get_state(), oracle.array("u_global"), what="floodplain")
+    if kernel == SPLIT224:
+        assert "K6" in op.kernel_info()  # the triangle tiles fit the compiled shape: no fallback
+    if kernel == FIXED224:
+        assert "K4" in op.kernel_info()
 
 
 @pytest.mark.parametrize("kernel", KERNELS)
@@ -81,6 +86,8 @@ def test_floodplain_hydrostatic_reconstruction(source_method, kernel):
         op.step_euler(case.dt, 100)
         oracle.step_euler(case.dt, 100)
         assert_state_close(op.get_state(), oracle.array("u_global"), what="floodplain HR")
+    if kernel == SPLIT224:
+        assert "K6" in op.kernel_info()
     assert (oracle.array("u_global").reshape(-1, 3)[:, 0] < 1e-7).sum() > 1000
 
 
