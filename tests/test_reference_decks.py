@@ -15,7 +15,7 @@ from rdycore_b200 import cases, io, rdy
 from rdycore_b200.operator import GATHER, TILED_FIXED
 
 from oracle import binding
-from util import assert_state_close, make_oracle
+from util import assert_state_close, celerity_momentum, make_oracle
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 FIX = os.path.join(HERE, "golden", "ref_fixtures")
@@ -102,4 +102,9 @@ def test_cuda_path_runs_the_reference_decks(name, kernel):
     assert r.RDyGetStep() == d["steps"]
     u = r.state()
     r.RDyDestroy()
-    assert_state_close(u, oracle.array("u_global"), what=name)
+    # ex2b_ic_file and levee.hr end (almost) at rest — |momentum| <= 0.008 under 1.5 to 7 m of water — so a momentum error relative to
+    # the momentum itself only measures the round-off of the pressure fluxes: the same C source with and without FMA contraction
+    # differs by 2.9e-10 / 7e-11 on those two decks (scratch/fma/sens4.py).  Momentum is therefore compared against
+    # max(|q|max, h sqrt(g h)); depth keeps the plain relative bar.
+    u_ref = oracle.array("u_global")
+    assert_state_close(u, u_ref, what=name, qscale_floor=celerity_momentum(u_ref))

@@ -24,7 +24,14 @@ def make_oracle(case, kind=None):
     return o
 
 
-def state_error(u_gpu: np.ndarray, u_ref: np.ndarray, tiny_h: float = 1e-7):
+def celerity_momentum(u_ref) -> float:
+    """h sqrt(g h) at the deepest cell: the momentum a unit-Froude flow would carry.  The scale of momentum round-off in states that
+    are (nearly) at rest, where the momentum itself is ~0 but every step still differences pressure fluxes g h^2 / 2."""
+    h = float(np.abs(np.asarray(u_ref).reshape(-1, 3)[:, 0]).max())
+    return h * np.sqrt(9.806 * h)
+
+
+def state_error(u_gpu: np.ndarray, u_ref: np.ndarray, tiny_h: float = 1e-7, qscale_floor: float = 0.0):
     """Parity metric.  Per component x in {h, hu, hv}: max over owned cells with h_ref >= 10 tiny_h of
     |x_gpu - x_ref| / max(|x_ref|, floor), with floor = 1e-3 * (max h for h; max momentum magnitude sqrt(hu^2+hv^2) for hu
     and hv, which mix through the edge-normal rotation).  Cells below 10 tiny_h are compared absolutely.
@@ -37,7 +44,7 @@ def state_error(u_gpu: np.ndarray, u_ref: np.ndarray, tiny_h: float = 1e-7):
     u_ref = np.asarray(u_ref).reshape(-1, 3)
     wet = u_ref[:, 0] >= 10 * tiny_h
     hscale = max(float(np.abs(u_ref[:, 0]).max()), 1e-300)
-    qscale = max(float(np.sqrt(u_ref[:, 1] ** 2 + u_ref[:, 2] ** 2).max()), 1e-300)
+    qscale = max(float(np.sqrt(u_ref[:, 1] ** 2 + u_ref[:, 2] ** 2).max()), qscale_floor, 1e-300)
     max_rel = normwise = 0.0
     for c, scale in ((0, hscale), (1, qscale), (2, qscale)):
         diff = np.abs(u_gpu[:, c] - u_ref[:, c])
@@ -50,10 +57,10 @@ def state_error(u_gpu: np.ndarray, u_ref: np.ndarray, tiny_h: float = 1e-7):
     return max_rel, max_abs, mismatch, normwise
 
 
-def assert_state_close(u_gpu, u_ref, tiny_h=1e-7, rel=REL_TOL, abs_dry=ABS_TOL_DRY, what=""):
+def assert_state_close(u_gpu, u_ref, tiny_h=1e-7, rel=REL_TOL, abs_dry=ABS_TOL_DRY, what="", qscale_floor=0.0):
     assert not np.isnan(np.asarray(u_ref)).any(), f"{what}: oracle produced NaN (bad test case)"
     assert not np.isnan(np.asarray(u_gpu)).any(), f"{what}: GPU produced NaN"
-    max_rel, max_abs, mismatch, normwise = state_error(u_gpu, u_ref, tiny_h)
+    max_rel, max_abs, mismatch, normwise = state_error(u_gpu, u_ref, tiny_h, qscale_floor)
     assert max_rel <= rel, f"{what}: max relative error {max_rel:.3e} > {rel:.1e}"
     assert normwise <= 1e-13, f"{what}: norm-wise error {normwise:.3e} > 1e-13"
     assert max_abs <= abs_dry, f"{what}: max absolute error on near-dry cells {max_abs:.3e} > {abs_dry:.1e}"
