@@ -1120,3 +1120,4 @@ extern "C" int rdyb_host_free(void *ptr) {
   if (ptr) CU(cudaFreeHost(ptr));
   return RDYB_SUCCESS;
 }
+#include "swe_forcing.cuh"

@@ -18,7 +18,12 @@ VECS = [
     "conditions/DamBreak_grid5x10_mixed_elements_wetdownstream.ic.int32.bin", "materials/manning_grid5x10.int32.bin",
     "materials/manning_grid5x10_mixed_elements.int32.bin", "conditions/levee_ic.int32.bin", "meshes/levee_elevation.int32.bin",
     "conditions/four_mounds_60x24.ic.int32.bin", "materials/manning_four_mound_60x24.int32.bin", "conditions/Houston1km.ic.int32.bin",
+    # forcing data: homogeneous rain and boundary series, two hourly rain rasters, unstructured rain / boundary data
+    "conditions/Houston1km.rain.int32.bin", "conditions/Houston1km.bc.int32.bin", "conditions/2017-08-26:00-00.int32.bin",
+    "conditions/2017-08-26:01-00.int32.bin", "conditions/simons-ss/simons_forcing_x_y.int32.bin", "conditions/simons-bc/simons_bc_x_y.int32.bin",
 ]
+RENAMED = {"conditions/simons-ss/2011-08-27:14-00.int32.bin": "simons-ss.2011-08-27:14-00.int32.bin",
+           "conditions/simons-bc/2011-08-27:14-00.int32.bin": "simons-bc.2011-08-27:14-00.int32.bin"}
 
 DECKS = ["ex2b_ic_file", "mixed_elements_ic_file", "four_mounds_60x24", "levee.hr", "Houston1km.DirichletBC"]
 
@@ -51,9 +56,9 @@ for m in MESHES:
     expected[m + "/side_set_offsets"] = np.cumsum([0] + [len(x) for x in se]).astype(np.int32)
     expected[m + "/side_elems"] = np.concatenate(se).astype(np.int32) if se else np.zeros(0, np.int32)
     expected[m + "/side_raw"] = np.concatenate(sr).astype(np.int32) if sr else np.zeros(0, np.int32)
-for v in VECS:
+for v in VECS + list(RENAMED):
     src = f"{SHARE}/{v}"
-    name = os.path.basename(v)
+    name = RENAMED.get(v, os.path.basename(v))
     shutil.copyfile(src, os.path.join(OUT, name))
     raw = open(src, "rb").read()
     if raw[:4] == (1211214).to_bytes(4, "big"):
