@@ -48,6 +48,8 @@ def parse_args():
     p.add_argument("--halo", default="p2p", choices=["p2p", "nccl"], help="N>1: peer-memory push over NVLink (CUDA IPC) or NCCL send/recv")
     p.add_argument("--eta0", type=float, default=None, help="initial lake level (default 18 m: ~55 %% of the cells wet; experiments only)")
     p.add_argument("--hr", action="store_true", help="config D: hydrostatic reconstruction + dam column")
+    p.add_argument("--second-order", action="store_true",
+                   help="secondary line: numerics.second_order (MUSCL, minmod) on a fully wet config C (eta0 60 m unless --eta0; the scheme has no dry-cell treatment)")
     return p.parse_args()
 
 
@@ -234,12 +236,17 @@ def run_b200_arm(args):
     if args.hr:
         case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=12.0, hr=True, px=px, py=py, rank=rank, dam_column=(2000.0, 28.0))
     else:
-        case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=18.0 if args.eta0 is None else args.eta0, px=px, py=py, rank=rank)
+        eta_default = 60.0 if args.second_order else 18.0
+        case = cases.floodplain(nx=args.nx * px, ny=ny * py, eta0=eta_default if args.eta0 is None else args.eta0, px=px, py=py, rank=rank)
+        if args.second_order:
+            case.config.reconstruction = cases.MUSCL_MINMOD
     halo = case.mesh.halo() if world > 1 else None
     op = Operator.from_case(case, device=local_rank, halo=halo)
     kernel = {"auto": TILED_FIXED, "gather": GATHER, "tiled": TILED, "async": TILED_ASYNC, "fixed": TILED_FIXED, "warp": WARP, "split": TILED_SPLIT}[args.kernel]
     kernel_name = {GATHER: "gather", TILED: "tiled", TILED_ASYNC: "tiled_async", TILED_FIXED: "tiled_fixed", WARP: "warp", TILED_SPLIT: "tiled_split"}[kernel]
     op.set_kernel(kernel, args.tile)
+    if args.second_order:
+        kernel_name = "gather_muscl"  # the second-order path runs muscl_gradient_kernel + K1 whatever kernel is selected
     op.set_options(courant=not args.no_courant)
     if world > 1:
         uid = [Operator.nccl_unique_id() if rank == 0 else None]
@@ -320,6 +327,8 @@ def run_b200_arm(args):
     if rank == 0:
         peak, peak_src = measured_peak()
         bytes_per_cell = 140 if args.hr else BYTES_PER_CELL_TRI
+        if args.second_order:  # + gradients written and read (48 + 48) + per-slot LS weights and face offsets (3 slots x 6 doubles)
+            bytes_per_cell += 96 + 144
         achieved = bytes_per_cell * n_owned / (ms_per_step * 1e-3) / 1e9  # this rank's kernel: per-GPU figure
         traffic = recorded_traffic(kernel_name + ("_hr" if args.hr else ""))
         line = {
@@ -328,7 +337,8 @@ def run_b200_arm(args):
             "config": {
                 "workload": ("config D: HR floodplain" if args.hr else "config C: synthetic unstructured triangle floodplain")
                 + f", {args.nx}x{ny}x2 = {2 * args.nx * ny} cells per GPU, bathymetry + Manning n + rain, reflecting walls, "
-                + ("XQ2018" if False else "semi-implicit") + " friction, forward Euler",
+                + ("XQ2018" if False else "semi-implicit") + " friction, forward Euler"
+                + (", second order (MUSCL, minmod), fully wet" if args.second_order else ""),
                 "cells_total": int(total_cells), "decomposition": (f"{px}x{py} blocks, 1 ghost layer, per-step halo: " + ("border cells pushed into the neighbours' ghost slots over NVLink (CUDA IPC peer memory)" if args.halo == "p2p" else "NCCL send/recv")) if world > 1 else "single GPU",
                 "kernel_info": kinfo,
                 "kernel": kernel_name, "tile_cells": args.tile if kernel != GATHER else None, "courant_diagnostic": not args.no_courant,
@@ -337,7 +347,7 @@ def run_b200_arm(args):
             },
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (traffic * n_owned if traffic else None), "peak_source": peak_src,
-                         "algorithmic_bytes_per_cell": bytes_per_cell, "kernel": "swe_%s_kernel" % kernel_name,
+                         "algorithmic_bytes_per_cell": bytes_per_cell, "kernel": "muscl_gradient_kernel + swe_gather_kernel<RECON>" if args.second_order else "swe_%s_kernel" % kernel_name,
                          "note": "per-GPU: algorithmic bytes of one launch / CUDA-event time per launch on the launching stream"},
             "e2e": e2e,
             "gpu_launches": int(launches),
