@@ -78,7 +78,8 @@ __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, d
 
 /* ComputeSWERoeEigenspectrum + the flux loop of ComputeSWERoeFlux, src/swe/swe_roe_flux_petsc.h:15-81, 108-128.
  * Inputs are (h,u,v,sqrt h) of the left and right state and the edge normal (cn,sn).  At least one of hl,hr must be > 0.
- * Re-association vs the reference: sqrt(g h) = sqrt(g) sqrt(h); chat and 1/chat from one rsqrt; one shared 1/(duml+dumr). */
+ * Re-association vs the reference: sqrt(g h) = sqrt(g) sqrt(h); chat and 1/chat from one rsqrt; one shared 1/(duml+dumr); the
+ * pressure terms and the w1/w3 columns of R |Lambda| dW are summed before they meet the normal (fewer multiplications). */
 template <bool FIX>
 __device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double vl, double sql, double hr, double ur, double vr, double sqr, double sn,
                                                   double cn, bool &needfix) {
@@ -101,9 +102,10 @@ __device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double v
   double a1 = fabs(uperp - chat);
   const double a2 = fabs(uperp);
   double a3 = fabs(uperp + chat);
-  /* critical flow fix, :55-69 */
-  const double da1 = fmax(0.0, 2.0 * ((uperpr - cr) - (uperpl - cl)));
-  const double da3 = fmax(0.0, 2.0 * ((uperpr + cr) - (uperpl + cl)));
+  /* critical flow fix, :55-69: 2 ((uperpr -+ cr) - (uperpl -+ cl)) = 2 (d(uperp) -+ d(c)), with d(uperp) = duperp */
+  const double dc = cr - cl;
+  const double da1 = fmax(0.0, 2.0 * (duperp - dc));
+  const double da3 = fmax(0.0, 2.0 * (duperp + dc));
   if (FIX) {
     if (a1 < da1) a1 = 0.5 * (a1 * a1 * swe_rcp(da1) + da1);
     if (a3 < da3) a3 = 0.5 * (a3 * a3 * swe_rcp(da3) + da3);
@@ -113,13 +115,15 @@ __device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double v
   }
   const double t = hhat * duperp * rchat;
   const double w1 = a1 * (0.5 * (dh - t)), w2 = a2 * (hhat * dupar), w3 = a3 * (0.5 * (dh + t));
-  const double pl = 0.5 * g * hl * hl, pr = 0.5 * g * hr * hr;
+  const double psum = 0.5 * g * (hl * hl + hr * hr); /* pl + pr */
   const double ql = uperpl * hl, qr = uperpr * hr;
   RoeFlux F;
-  /* F = 0.5*(FL + FR - R |Lambda| dW) with R = [[1,0,1],[uhat-chat*cn,-sn,uhat+chat*cn],[vhat-chat*sn,cn,vhat+chat*sn]] */
-  F.f0 = 0.5 * (ql + qr - w1 - w3);
-  F.f1 = 0.5 * ((ul * ql + pl * cn) + (ur * qr + pr * cn) - (uhat - chat * cn) * w1 - (-sn) * w2 - (uhat + chat * cn) * w3);
-  F.f2 = 0.5 * ((vl * ql + pl * sn) + (vr * qr + pr * sn) - (vhat - chat * sn) * w1 - cn * w2 - (vhat + chat * sn) * w3);
+  /* F = 0.5*(FL + FR - R |Lambda| dW) with R = [[1,0,1],[uhat-chat*cn,-sn,uhat+chat*cn],[vhat-chat*sn,cn,vhat+chat*sn]];
+   * the w1 and w3 columns are summed as uhat (w1 + w3) + chat cn (w3 - w1) (and the same with vhat, sn) */
+  const double ws = w1 + w3, wd = chat * (w3 - w1);
+  F.f0 = 0.5 * (ql + qr - ws);
+  F.f1 = 0.5 * (ul * ql + ur * qr + psum * cn - uhat * ws - wd * cn + sn * w2);
+  F.f2 = 0.5 * (vl * ql + vr * qr + psum * sn - vhat * ws - wd * sn - cn * w2);
   F.amax = chat + fabs(uperp);
   return F;
 }
