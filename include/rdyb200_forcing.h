@@ -61,6 +61,14 @@ int rdyb_operator_fill_boundary_values(RdybOperator op, int32_t b, double h, dou
 /* Dirichlet values of boundary b as the operator holds them: values[3 * e + c] */
 int rdyb_operator_get_boundary_values(RdybOperator op, int32_t b, int32_t num_edges, double *values);
 
+
+/* ---- time series (src/time_series.c) ----
+ * (h, hu, hv) at n observation sites (owned cell ids), values[3 i + c]: WriteObservations' VecScatter, :400-445, without moving the
+ * whole solution to the host */
+int rdyb_operator_get_state_at(RdybOperator op, int32_t n, const int32_t *owned_cell_ids, double *values);
+/* zero the accumulated boundary fluxes once they have been written: ResetAccumulatedBoundaryFluxes, :508-527 */
+int rdyb_operator_reset_boundary_fluxes(RdybOperator op);
+
 #ifdef __cplusplus
 }
 #endif

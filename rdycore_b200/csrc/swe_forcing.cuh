@@ -79,6 +79,13 @@ __global__ void dataset_gather_boundary_kernel(int32_t ne, const int32_t *__rest
   const int64_t k = offset + 3 * (int64_t)map[e];
   bval[e] = data[k]; bval[comp_stride + e] = data[k + 1]; bval[2 * comp_stride + e] = data[k + 2];
 }
+/* out[3 i + c] = state[c][sites[i]] : observation sites */
+__global__ void sample_state_kernel(int32_t n, const int32_t *__restrict__ sites, const double *__restrict__ state, int64_t stride, double *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t d = sites[i];
+  out[3 * (int64_t)i] = state[d]; out[3 * (int64_t)i + 1] = state[stride + d]; out[3 * (int64_t)i + 2] = state[2 * stride + d];
+}
 __global__ void fill_kernel(int64_t n, double v, double *__restrict__ dst) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[i] = v;
@@ -279,6 +286,35 @@ extern "C" int rdyb_operator_get_boundary_values(RdybOperator op, int32_t b, int
   CU(cudaStreamSynchronize(op->stream));
   for (int32_t e = 0; e < ne; ++e)
     for (int c = 0; c < 3; ++c) values[3 * (size_t)e + c] = tmp[(size_t)c * ne + e];
+  return RDYB_SUCCESS;
+}
+
+/* time series (src/time_series.c): the state at n observation sites without downloading the whole solution (WriteObservations,
+ * :400-445, a VecScatter of u_global in the reference), and the reset of the boundary-flux accumulators after they have been
+ * written (ResetAccumulatedBoundaryFluxes, :508-527) */
+extern "C" int rdyb_operator_get_state_at(RdybOperator op, int32_t n, const int32_t *owned_cell_ids, double *values) {
+  RDYB_CHECK(op && (n == 0 || (owned_cell_ids && values)), RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(n <= op->N, RDYB_ERR_ARG_SIZ, "more sites (%d) than owned cells (%d)", n, op->N);
+  if (n == 0) return RDYB_SUCCESS;
+  CU(cudaSetDevice(op->device));
+  std::vector<int32_t> idx((size_t)n);
+  for (int32_t i = 0; i < n; ++i) {
+    RDYB_CHECK(owned_cell_ids[i] >= 0 && owned_cell_ids[i] < op->N, RDYB_ERR_USER, "owned cell id %d out of range", owned_cell_ids[i]);
+    idx[i] = op->L.owned_to_dev[owned_cell_ids[i]];
+  }
+  CU(cudaMemcpyAsync(op->stage_idx, idx.data(), sizeof(int32_t) * n, cudaMemcpyHostToDevice, op->stream));
+  sample_state_kernel<<<grid_for(n, 256), 256, 0, op->stream>>>(n, op->stage_idx, op->state[op->cur], op->stride, op->stage);
+  LAUNCHED();
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * 3 * (size_t)n, cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_reset_boundary_fluxes(RdybOperator op) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  CU(cudaSetDevice(op->device));
+  if (op->bacc && op->nbe > 0) CU(cudaMemsetAsync(op->bacc, 0, sizeof(double) * 3 * (size_t)op->nbe, op->stream));
   return RDYB_SUCCESS;
 }
 #endif

@@ -91,3 +91,15 @@ def get_boundary_values(op, b, num_edges) -> np.ndarray:
     out = np.zeros((num_edges, 3))
     check(lib().rdyb_operator_get_boundary_values(op._h, C.c_int32(b), C.c_int32(num_edges), out.ctypes.data_as(_D)))
     return out
+
+
+def get_state_at(op, owned_cell_ids) -> np.ndarray:
+    """(h, hu, hv) at observation sites: [n, 3]"""
+    ids = np.ascontiguousarray(owned_cell_ids, dtype=np.int32)
+    out = np.zeros((ids.size, 3))
+    check(lib().rdyb_operator_get_state_at(op._h, C.c_int32(ids.size), ids.ctypes.data_as(_I), out.ctypes.data_as(_D)))
+    return out
+
+
+def reset_boundary_fluxes(op):
+    check(lib().rdyb_operator_reset_boundary_fluxes(op._h))

@@ -200,3 +200,27 @@ def test_houston_run_forced_on_the_device_equals_the_host_forced_run():
     uh, ud = host.get_state(), dev.get_state()
     assert not np.isnan(uh).any() and np.array_equal(uh, ud)
     assert np.abs(uh - case.u0).max() > 1e-3
+
+
+@pytest.mark.gpu
+def test_observation_sites_and_boundary_flux_reset():
+    """time_series.c: observations are the state at a few cells; accumulated boundary fluxes restart from zero after each write."""
+    case, _, _ = _houston()
+    b = next(i for i, bd in enumerate(case.boundaries) if bd.bc_type == cases.DIRICHLET)
+    ne = len(case.boundaries[b].edge_ids)
+    op = Operator.from_case(case)
+    op.set_options(courant=True, boundary_fluxes=True)
+    op.step_euler(case.dt, 20)
+    u = op.get_state()
+    sites = np.array([0, 17, 1234, op.num_owned - 1, 17], np.int32)
+    assert np.array_equal(forcing.get_state_at(op, sites), u[sites])
+    with pytest.raises(RuntimeError, match="out of range"):
+        forcing.get_state_at(op, [op.num_owned])
+    acc = op.get_boundary_fluxes(b, ne, accumulated=True)
+    assert np.abs(acc).max() > 0.0
+    forcing.reset_boundary_fluxes(op)
+    assert np.abs(op.get_boundary_fluxes(b, ne, accumulated=True)).max() == 0.0
+    op.step_euler(case.dt, 1)
+    one = op.get_boundary_fluxes(b, ne, accumulated=True)
+    inst = op.get_boundary_fluxes(b, ne, accumulated=False)
+    assert np.allclose(one, case.dt * inst, rtol=1e-14, atol=0.0)
