@@ -93,6 +93,31 @@ def moving_rhs_case():
     return case
 
 
+def second_order(reconstruction, triangles):
+    """numerics.second_order (MUSCL) on fully wet cases: the quad dam break, or the triangle floodplain under 40 m of water with a
+    rough momentum field (the scheme has no dry-cell treatment, the reference returns NaN there)."""
+    def build():
+        if triangles:
+            case = cases.floodplain(nx=20, ny=16, eta0=40.0)
+            rng = np.random.default_rng(11)
+            n = case.u0.shape[0]
+            case.u0[:, 1] = rng.normal(0, 0.3, n) * case.u0[:, 0]
+            case.u0[:, 2] = rng.normal(0, 0.3, n) * case.u0[:, 0]
+        else:
+            case = cases.dam_break_quads(nx=24, ny=12, source_method=cases.SEMI_IMPLICIT)
+        case.config.reconstruction = reconstruction
+        return case
+    return build
+
+
+def reference_deck(name):
+    """the reference's own decks on its own mesh / IC / Manning / elevation files (tests/test_reference_decks.py)"""
+    def build():
+        from test_reference_decks import deck_case
+        return deck_case(name)
+    return build
+
+
 # name -> (builder, "euler" | "rk4" | "rhs", nsteps)
 GOLDEN = {
     "dam_break_xq2018": (dam_break(cases.IMPLICIT_XQ2018), "euler", 200),
@@ -105,6 +130,19 @@ GOLDEN = {
     "mixed_elements": (mixed_elements, "euler", 200),
     "floodplain_rk4": (floodplain_rain, "rk4", 30),
     "moving_rhs": (moving_rhs_case, "rhs", 1),
+    # second order: minmod and van Leer limiters, unlimited; Euler and RK4
+    "muscl_minmod_quads": (second_order(cases.MUSCL_MINMOD, False), "euler", 150),
+    "muscl_none_quads": (second_order(cases.MUSCL_NONE, False), "euler", 150),
+    "muscl_vanleer_quads": (second_order(cases.MUSCL_VANLEER, False), "euler", 150),
+    "muscl_minmod_triangles": (second_order(cases.MUSCL_MINMOD, True), "euler", 100),
+    "muscl_vanleer_triangles_rk4": (second_order(cases.MUSCL_VANLEER, True), "rk4", 30),
+    "muscl_minmod_rhs": (second_order(cases.MUSCL_MINMOD, True), "rhs", 1),
+    # the reference's decks and fixture files
+    "deck_ex2b_ic_file": (reference_deck("ex2b_ic_file"), "euler", 300),
+    "deck_mixed_elements_ic_file": (reference_deck("mixed_elements_ic_file"), "euler", 300),
+    "deck_four_mounds_60x24": (reference_deck("four_mounds_60x24"), "euler", 25),
+    "deck_levee_hr": (reference_deck("levee.hr"), "euler", 200),
+    "deck_houston1km": (reference_deck("Houston1km.DirichletBC"), "euler", 140),
 }
 
 

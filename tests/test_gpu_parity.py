@@ -11,7 +11,7 @@ from rdycore_b200 import cases
 from rdycore_b200.mesh import HostMesh
 from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP, Operator
 
-from util import REL_TOL, assert_state_close, make_oracle, state_error
+from util import REL_TOL, assert_state_close, celerity_momentum, make_oracle, state_error
 
 pytestmark = pytest.mark.gpu
 
@@ -284,7 +284,9 @@ def test_cuda_path_against_reference_golden_vectors(name, kernel):
         op.step_euler(case.dt, nsteps)
     else:
         op.step_rk4(2 * case.dt, nsteps)
-    assert_state_close(op.get_state(), golden[f"{name}/u"], what=f"golden {name}")
+    # decks that end (almost) at rest: momentum against the celerity momentum (tests/test_reference_decks.py explains why)
+    floor = celerity_momentum(golden[f"{name}/u"]) if name.startswith("deck_") else 0.0
+    assert_state_close(op.get_state(), golden[f"{name}/u"], what=f"golden {name}", qscale_floor=floor)
     for b, bd in enumerate(case.boundaries):
         key = f"{name}/bacc{b}"
         if key in golden.files and len(bd.edge_ids):
