@@ -1,7 +1,7 @@
 """Copies the small mesh / initial-condition / material fixtures of the reference's SWE decks (share/meshes, share/conditions,
 share/materials: binary DATA files, no code) into tests/golden/ref_fixtures/ and records what an independent parser (scipy's
 NetCDF-3 reader, numpy for the PETSc binary Vecs) makes of them in ref_fixtures.npz — the expected values of
-tests/test_io_formats.py — together with the decks (driver/tests/swe_roe/*.yaml) that use them, into tests/decks/ref/.  The tests then never touch /root/reference (it does not exist on the GPU box).
+tests/test_io_formats.py — together with the scalar sections of the decks (driver/tests/swe_roe/*.yaml) that use them, into tests/decks/ref/.  The tests then never touch /root/reference (it does not exist on the GPU box).
 Run in the build container:  python tests/golden/make_ref_fixtures.py"""
 import os
 import shutil
@@ -29,8 +29,21 @@ DECKS = ["ex2b_ic_file", "mixed_elements_ic_file", "four_mounds_60x24", "levee.h
 
 os.makedirs(OUT, exist_ok=True)
 os.makedirs(os.path.join(HERE, "..", "decks", "ref"), exist_ok=True)
-for d in DECKS:  # the reference's own input decks, unmodified (configuration data)
-    shutil.copyfile(f"/root/reference/driver/tests/swe_roe/{d}.yaml", os.path.join(HERE, "..", "decks", "ref", d + ".yaml"))
+KEEP = ("physics", "numerics", "time", "grid")  # the sections RDyCreate reads here; regions / materials / conditions / output go through setters
+for d in DECKS:
+    lines, keep = [], False
+    for ln in open(f"/root/reference/driver/tests/swe_roe/{d}.yaml"):
+        if not ln.strip() or ln.lstrip().startswith("#"):
+            continue
+        if not ln[0].isspace():
+            keep = ln.split(":")[0].strip() in KEEP
+        if keep:
+            lines.append(ln.rstrip() + "\n")
+    with open(os.path.join(HERE, "..", "decks", "ref", d + ".yaml"), "w") as f:
+        f.write(f"# physics / numerics / time / grid sections of the reference deck driver/tests/swe_roe/{d}.yaml, values unchanged\n"
+                "# (written by tests/golden/make_ref_fixtures.py).  Its regions, materials, initial and boundary conditions are applied by\n"
+                "# tests/test_reference_decks.py through the setters, from the fixture files the deck names.\n")
+        f.writelines(lines)
 expected = {}
 for m in MESHES:
     src = f"{SHARE}/meshes/{m}.exo"

@@ -1,8 +1,8 @@
 """The reference's own SWE decks on the reference's own fixture files: driver/tests/swe_roe/{ex2b_ic_file,
 mixed_elements_ic_file,four_mounds_60x24,levee.hr,Houston1km.DirichletBC}.yaml with their Exodus meshes, PETSc-binary initial
 conditions, Manning files and cell elevations (tests/golden/ref_fixtures/, tests/decks/ref/, copied by
-tests/golden/make_ref_fixtures.py).  The files go through the C readers of include/rdyb200_io.h, the scalar sections of the
-UNMODIFIED decks through RDyCreate; the list sections (regions, materials, conditions) are applied here through the setters.
+tests/golden/make_ref_fixtures.py).  The files go through the C readers of include/rdyb200_io.h, the physics / numerics / time sections of
+the decks (values unchanged) through RDyCreate; the list sections (regions, materials, conditions) are applied here through the setters.
 
 CPU: restated oracle == the reference's own code, bitwise, on these meshes.  GPU: CUDA path == oracle at the stated tolerance
 after the deck's own number of steps."""
@@ -77,7 +77,7 @@ def test_port_equals_reference_on_the_reference_decks(name):
 @pytest.mark.parametrize("kernel", [(GATHER, 0), (TILED_FIXED, 224), (TILED_FIXED, 256)])
 @pytest.mark.parametrize("name", sorted(DECKS))
 def test_cuda_path_runs_the_reference_decks(name, kernel):
-    """RDyCreate(<the reference's deck>) -> RDySetup -> RDyAdvance until RDyFinished, against the oracle."""
+    """RDyCreate(<the deck's physics / numerics / time sections>) -> RDySetup -> RDyAdvance until RDyFinished, against the oracle."""
     case = deck_case(name)
     d = DECKS[name]
     oracle = make_oracle(case)
