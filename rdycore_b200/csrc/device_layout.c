@@ -343,7 +343,15 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
   memset(T, 0, sizeof(*T));
   const int32_t N = L->n_owned, NI = L->n_interior, W = L->width, TC = tile_cells;
   const size_t S = (size_t)L->stride;
-  const int32_t nt_int = (NI + TC - 1) / TC, nt_fr = (N - NI + TC - 1) / TC, nt = nt_int + nt_fr;
+  /* frontier cells (neighbours of ghosts) are cut into SHORT tiles: a strip along a partition border has up to `width` outside
+   * neighbours per cell, so a full-size tile of it would need several hundred halo cells and could only run on the general
+   * kernel in a launch of its own.  With at most 80 / width cells (a multiple of 8, for the 16-byte slices) a frontier tile has
+   * <= 80 halo cells and <= 80 edges and fits every compiled tile shape: interior and frontier run in ONE launch (K4 waits for the
+   * neighbours' border cells inside the kernel, swe_tiled_fixed.cuh).  There are few of them (~0.05 % of the cells at 10 M). */
+  int32_t TCF = (80 / (W > 0 ? W : 1)) & ~7;
+  if (TCF < 8) TCF = 8;
+  if (TCF > TC) TCF = TC;
+  const int32_t nt_int = (NI + TC - 1) / TC, nt_fr = (N - NI + TCF - 1) / TCF, nt = nt_int + nt_fr;
   T->tile_cells = TC; T->num_tiles = nt; T->num_interior_tiles = nt_int;
   LALLOC(T->tile_cell_begin, nt + 1); LALLOC(T->halo_offsets, nt + 1); LALLOC(T->edge_offsets, nt + 1);
   LALLOC(T->tile_desc, 8 * (size_t)nt);
@@ -352,9 +360,9 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
   LALLOC(tmp_halo, (size_t)TC * RDYB_ELL_WIDTH); LALLOC(slot_edge, (size_t)TC * RDYB_ELL_WIDTH);
   int64_t hcap = 0, ecap = 0, nh = 0, ne = 0;
   for (int32_t t = 0; t < nt; ++t) {
-    const int32_t cb = t < nt_int ? t * TC : NI + (t - nt_int) * TC;
-    const int32_t lim = t < nt_int ? NI : N;
-    const int32_t ce = cb + TC < lim ? cb + TC : lim, ncell = ce - cb;
+    const int32_t cb = t < nt_int ? t * TC : NI + (t - nt_int) * TCF;
+    const int32_t lim = t < nt_int ? NI : N, span = t < nt_int ? TC : TCF;
+    const int32_t ce = cb + span < lim ? cb + span : lim, ncell = ce - cb;
     /* tile starts are padded to 4 entries (16 bytes for the int32/uint32 arrays, 32 for the doubles) so that a tile's slice
      * of every per-tile array can be fetched with one bulk async copy */
     while (nh & 3) { GROW(T->halo_cells, hcap, nh + 1); T->halo_cells[nh++] = 0; }

@@ -124,6 +124,7 @@ struct RdybOperator_ {
   bool mom_src = false; /* any momentum external source set */
   /* peer-memory halo (Euler fast path) */
   bool p2p = false;
+  bool wait_in_kernel = false; /* set around the one-launch p2p step: K4 waits for the neighbours inside the kernel */
   PeerTable ptab;
   unsigned int p2p_epoch = 0;
   unsigned int *p2p_flags = nullptr; /* [RDYB_MAX_PEERS] counters raised by the neighbours, + 1 status word */
@@ -563,24 +564,28 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
   if (op->kernel_kind >= 1 && op->has_tiled && !op->recon) { /* the second-order path runs on K1 */
     /* interior tiles and frontier tiles (thin strips along the partition border, with many more outside neighbours) are
      * launched separately so that each part can use the most specialised kernel its tiles fit */
-    if (begin < op->NI && end > op->NI) {
+    SweArgs t;
+    fill_args(op, t, in, out, dt);
+    /* frontier tiles are short (device_layout.c), so they normally fit K4's compiled shapes too: one launch for both parts */
+    const bool whole_fits = op->kernel_kind == 3 && tiled_fixed_applicable(op->T.tile_cells, op->T.max_halo, op->T.max_edges, t);
+    if (begin < op->NI && end > op->NI && !whole_fits) {
       RDYB_CALL(launch_cells(op, in, out, dt, euler, begin, op->NI, cslot0));
       return launch_cells(op, in, out, dt, euler, op->NI, end, cslot0);
     }
-    SweArgs t;
-    fill_args(op, t, in, out, dt);
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile, indexed by tile number */
     const bool interior = end <= op->NI;
     const int mh = interior ? op->T.max_halo_interior : op->T.max_halo, me = interior ? op->T.max_edges_interior : op->T.max_edges;
+    FixedWait fw = {op->ptab.num_peers, op->p2p_epoch, op->p2p_flags, reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS)};
+    const FixedWait *wait = op->wait_in_kernel ? &fw : nullptr;
     op->warp_used = op->kernel_kind == 4 && op->has_warp && warp_applicable(op->WL, t);
     if (op->warp_used) { op->last_kernel = "swe_warp_kernel (K5)"; RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream)); }
     else if (op->kernel_kind == 5 && tiled_split_applicable(op->td, op->T.tile_cells, mh, me, t)) {
       if (interior || op->NI == 0) op->last_kernel = "swe_tiled_split_kernel (K6)";
       RDYB_CALL(tiled_split_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
     } else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T.tile_cells, mh, me, t)) {
-      if (interior || op->NI == 0) op->last_kernel = "swe_tiled_fixed_kernel (K4)";
-      RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, mh, me, op->stream));
+      if (begin < op->NI || op->NI == 0) op->last_kernel = "swe_tiled_fixed_kernel (K4)";
+      RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, mh, me, op->stream, wait));
     } else if (op->kernel_kind >= 2) {
       if (interior || op->NI == 0) op->last_kernel = "swe_tiled_async_kernel (K3)";
       RDYB_CALL(tiled_async_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
@@ -944,8 +949,22 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
     /* peer-memory halo: the two state buffers alternate, so a neighbour's push for step s+1 lands in the buffer this rank
      * does not read during step s, and its counter (raised after its frontier kernel) orders everything else */
     RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+    /* K4 over the whole range: the wait for the neighbours' border cells happens inside the kernel, before a CTA's first frontier tile */
+    SweArgs probe;
+    fill_args(op, probe, op->state[0], op->state[1], dt);
+    const bool one_launch = op->has_tiled && op->kernel_kind == 3 && op->NI < op->N && !getenv("RDYB_P2P_SPLIT_LAUNCH") &&
+                            tiled_fixed_applicable(op->T.tile_cells, op->T.max_halo, op->T.max_edges, probe);
     for (int32_t s = 0; s < nsteps; ++s) {
       double *in = op->state[op->cur], *out = op->state[op->cur ^ 1];
+      if (one_launch) {
+        op->wait_in_kernel = true;
+        const int rc = launch_cells(op, in, out, dt, true, 0, op->N, 0);
+        op->wait_in_kernel = false;
+        RDYB_CALL(rc);
+        op->cur ^= 1;
+        if (s + 1 < nsteps) RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+        continue;
+      }
       RDYB_CALL(launch_cells(op, in, out, dt, true, 0, op->NI, 0));                       /* interior cells: no ghost needed */
       RDYB_CALL(p2p_wait(op));                                                          /* neighbours' border cells have landed */
       RDYB_CALL(launch_cells(op, in, out, dt, true, op->NI, op->N, op->ncblocks_interior)); /* frontier cells */

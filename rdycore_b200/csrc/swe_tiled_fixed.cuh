@@ -59,6 +59,13 @@ struct FixedSmem {
 struct FixedArgs {
   TiledArgs t;
   int32_t tile_begin, tile_end;
+  /* multi-GPU, peer-memory halo: tiles >= wait_tile (the frontier tiles, numbered after the interior ones) stage ghost cells, so
+   * the producer warp of a CTA waits until every neighbour's counter has reached wait_epoch before it issues the first of them;
+   * interior and frontier then run in one launch.  wait_tile = INT32_MAX: no wait. */
+  int32_t wait_tile = 0x7fffffff, wait_peers = 0;
+  unsigned int wait_epoch = 0;
+  const unsigned int *wait_flags = nullptr;
+  int *wait_status = nullptr;
 };
 
 template <int NCONS>
@@ -104,8 +111,22 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
     int hidx[HK];
 #pragma unroll
     for (int k = 0; k < HK; ++k) { const int t = lane + 32 * k; hidx[k] = t < d1.y ? __ldg(p.halo_cells + d1.x + t) : 0; }
+    bool waited = false;
     for (int it = 0; tile < q.tile_end; tile += G, ++it) {
       const int s = it % NS;
+      if (tile >= q.wait_tile && !waited) { /* halo_wait_kernel, inside the step (swe_kernels.cuh) */
+        if (lane < q.wait_peers) {
+          const volatile unsigned int *f = q.wait_flags + lane;
+          const long long t0 = clock64();
+          while ((int)(*f - q.wait_epoch) < 0) {
+            __nanosleep(100);
+            if (clock64() - t0 > 6000000000ll) { atomicExch(q.wait_status, 1 + lane); break; } /* ~3 s: a hung peer must not hang this GPU */
+          }
+        }
+        __syncwarp();
+        __threadfence_system();
+        waited = true;
+      }
       /* prefetch: descriptor two tiles ahead, halo index list one tile ahead */
       int4 nn0 = make_int4(0, 0, 0, 0);
       int2 nn1 = make_int2(0, 0);
@@ -374,8 +395,15 @@ static inline bool tiled_fixed_applicable(int tc, int mh, int me, const SweArgs 
   return fixed_fits_t(tc, mh, me) || fixed_fits_a(tc, mh, me) || fixed_fits_s(tc, mh, me);
 }
 
+struct FixedWait {
+  int32_t peers;
+  unsigned int epoch;
+  const unsigned int *flags;
+  int *status;
+};
+
 static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a, int32_t n_interior,
-                                     bool euler, bool courant, int max_halo, int max_edges, cudaStream_t stream) {
+                                     bool euler, bool courant, int max_halo, int max_edges, cudaStream_t stream, const FixedWait *wait = nullptr) {
   FixedArgs q;
   TiledArgs &p = q.t;
   p.a = a;
@@ -389,6 +417,9 @@ static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T
   p.tile_order = d.order;
   if (d.order) { if (d.sub_begin > q.tile_begin) q.tile_begin = d.sub_begin; if (d.sub_end < q.tile_end) q.tile_end = d.sub_end; }
   if (q.tile_end <= q.tile_begin) return RDYB_SUCCESS;
+  if (wait && wait->peers > 0 && !d.order && q.tile_end > T.num_interior_tiles) {
+    q.wait_tile = T.num_interior_tiles; q.wait_peers = wait->peers; q.wait_epoch = wait->epoch; q.wait_flags = wait->flags; q.wait_status = wait->status;
+  }
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
   const int nt = q.tile_end - q.tile_begin;
