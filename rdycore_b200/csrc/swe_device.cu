@@ -130,6 +130,15 @@ struct RdybOperator_ {
   unsigned int *p2p_flags = nullptr; /* [RDYB_MAX_PEERS] counters raised by the neighbours, + 1 status word */
   void *p2p_opened[3 * RDYB_MAX_PEERS];
   int p2p_nopened = 0;
+  /* fused push (K4 stores the border cells of each finished frontier tile into the neighbours itself; swe_tiled_fixed.cuh) */
+  struct {
+    bool built = false, active = false;
+    int2 *range = nullptr;      /* [num_tiles] send entries of each tile */
+    int32_t *src = nullptr, *rs = nullptr, *order = nullptr;
+    double **dst[2] = {nullptr, nullptr}; /* per ping-pong buffer */
+    unsigned int *counter = nullptr;
+    unsigned int send_tiles = 0, launches = 0;
+  } fpush;
   /* comm */
   ncclComm_t comm = nullptr;
   int32_t nranks = 1, rank = 0;
@@ -167,6 +176,13 @@ extern "C" int64_t rdyb_kernel_launch_count(void) { return g_launches.load(); }
 
 static int grid_for(int64_t n, int block) { return (int)((n + block - 1) / block); }
 
+static void fpush_release(RdybOperator op) { /* the send lists depend on the tiling and on the peer table */
+  void *fp[] = {op->fpush.range, op->fpush.src, op->fpush.rs, op->fpush.order, op->fpush.dst[0], op->fpush.dst[1], op->fpush.counter};
+  for (void *q : fp)
+    if (q) cudaFree(q);
+  op->fpush = {};
+}
+
 extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   if (!pop || !*pop) return RDYB_SUCCESS;
   RdybOperator op = *pop;
@@ -175,6 +191,7 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   if (op->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(op->comm);
   for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]);
   if (op->p2p_flags) cudaFree(op->p2p_flags);
+  fpush_release(op);
   void *ptrs[] = {op->state[0], op->state[1], op->F, op->src, op->mann, op->fdiv, op->prim, op->inv_area, op->area, op->dzdx, op->dzdy, op->zc,
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
                   op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
@@ -332,6 +349,7 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
       rdyb_tiled_layout_free(&op->T);
       op->has_tiled = false;
       pipe_release(op);
+      fpush_release(op);
     }
     if (!op->has_tiled) {
       RDYB_CALL(rdyb_tiled_layout_build(&op->L, tile_cells, &op->T));
@@ -577,6 +595,12 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     const bool interior = end <= op->NI;
     const int mh = interior ? op->T.max_halo_interior : op->T.max_halo, me = interior ? op->T.max_edges_interior : op->T.max_edges;
     FixedWait fw = {op->ptab.num_peers, op->p2p_epoch, op->p2p_flags, reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS)};
+    if (op->wait_in_kernel && op->fpush.active && euler) { /* this launch also sends: the epoch the neighbours wait for next */
+      const int buf = out == op->state[1];
+      fw.order = op->fpush.order; fw.push_range = op->fpush.range; fw.push_src = op->fpush.src; fw.push_dst = op->fpush.dst[buf]; fw.push_rs = op->fpush.rs;
+      fw.push_counter = op->fpush.counter; fw.push_target = ++op->fpush.launches * op->fpush.send_tiles;
+      fw.push_epoch = op->p2p_epoch + 1; fw.push_flag = op->ptab.flag;
+    }
     const FixedWait *wait = op->wait_in_kernel ? &fw : nullptr;
     op->warp_used = op->kernel_kind == 4 && op->has_warp && warp_applicable(op->WL, t);
     if (op->warp_used) { op->last_kernel = "swe_warp_kernel (K5)"; RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream)); }
@@ -738,6 +762,7 @@ extern "C" int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_
   t.send_begin[L.num_peers] = L.num_peers ? L.send_offsets[L.num_peers] : 0;
   op->p2p = L.num_peers > 0;
   op->p2p_epoch = 0;
+  fpush_release(op);
   return RDYB_SUCCESS;
 }
 
@@ -748,6 +773,47 @@ static int p2p_push(RdybOperator op, const double *state, int buf) {
   CU(cudaGetLastError());
   return RDYB_SUCCESS;
 }
+/* send lists per frontier tile for the fused push: entry = {device cell, the neighbour's ghost slot in either buffer, its stride} */
+static int p2p_fused_build(RdybOperator op) {
+  if (op->fpush.built) return RDYB_SUCCESS;
+  const RdybLayout &L = op->L;
+  const auto &T = op->T;
+  const int32_t nt = T.num_tiles, nit = T.num_interior_tiles, ns = L.send_offsets[L.num_peers];
+  std::vector<int32_t> tile_of(ns), count(nt + 1, 0);
+  for (int32_t i = 0; i < ns; ++i) {
+    const int32_t c = L.send_cells[i];
+    const int32_t t = (int32_t)(std::upper_bound(T.tile_cell_begin, T.tile_cell_begin + nt + 1, c) - T.tile_cell_begin) - 1;
+    RDYB_CHECK(t >= nit && t < nt, RDYB_ERR_USER, "fused push: a send cell lies outside the frontier tiles");
+    tile_of[i] = t;
+    count[t + 1]++;
+  }
+  for (int32_t t = 0; t < nt; ++t) count[t + 1] += count[t];
+  std::vector<int2> range(nt);
+  unsigned int send_tiles = 0;
+  for (int32_t t = 0; t < nt; ++t) { range[t] = make_int2(count[t], count[t + 1] - count[t]); send_tiles += range[t].y > 0; }
+  std::vector<int32_t> src(ns), rs(ns), fill(count.begin(), count.end() - 1), order(nt);
+  std::vector<double *> dst0(ns), dst1(ns);
+  for (int p = 0; p < L.num_peers; ++p)
+    for (int32_t i = L.send_offsets[p]; i < L.send_offsets[p + 1]; ++i) {
+      const int32_t k = fill[tile_of[i]]++, g = op->ptab.ghost0[p] + (i - L.send_offsets[p]);
+      src[k] = L.send_cells[i]; rs[k] = op->ptab.stride[p];
+      dst0[k] = op->ptab.state[p][0] + g; dst1[k] = op->ptab.state[p][1] + g;
+    }
+  for (int32_t t = 0; t < nt; ++t) order[t] = t < nt - nit ? nit + t : t - (nt - nit); /* frontier tiles first */
+  RDYB_CALL(upload(&op->fpush.range, range.data(), (size_t)nt));
+  RDYB_CALL(upload(&op->fpush.src, src.data(), (size_t)ns));
+  RDYB_CALL(upload(&op->fpush.rs, rs.data(), (size_t)ns));
+  RDYB_CALL(upload(&op->fpush.order, order.data(), (size_t)nt));
+  RDYB_CALL(upload(&op->fpush.dst[0], dst0.data(), (size_t)ns));
+  RDYB_CALL(upload(&op->fpush.dst[1], dst1.data(), (size_t)ns));
+  RDYB_CALL(dalloc(&op->fpush.counter, 1));
+  CU(cudaMemset(op->fpush.counter, 0, sizeof(unsigned int)));
+  op->fpush.send_tiles = send_tiles;
+  op->fpush.launches = 0;
+  op->fpush.built = true;
+  return RDYB_SUCCESS;
+}
+
 static int p2p_wait(RdybOperator op) {
   halo_wait_kernel<<<1, 32, 0, op->stream>>>(op->p2p_flags, op->ptab.num_peers, op->p2p_epoch, 6000000000ll /* ~3 s */,
                                             reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS));
@@ -954,15 +1020,22 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
     fill_args(op, probe, op->state[0], op->state[1], dt);
     const bool one_launch = op->has_tiled && op->kernel_kind == 3 && op->NI < op->N && !getenv("RDYB_P2P_SPLIT_LAUNCH") &&
                             tiled_fixed_applicable(op->T.tile_cells, op->T.max_halo, op->T.max_edges, probe);
+    /* fused push: the kernel of step s also delivers the border cells of step s+1 (and raises epoch + 1), so the loop has no
+     * push kernel at all; the explicit push above only primes the first step of the call */
+    const bool fused = one_launch && op->L.send_offsets[op->L.num_peers] > 0 && !getenv("RDYB_P2P_NO_FUSED_PUSH");
+    if (fused) RDYB_CALL(p2p_fused_build(op));
     for (int32_t s = 0; s < nsteps; ++s) {
       double *in = op->state[op->cur], *out = op->state[op->cur ^ 1];
       if (one_launch) {
         op->wait_in_kernel = true;
+        op->fpush.active = fused;
         const int rc = launch_cells(op, in, out, dt, true, 0, op->N, 0);
         op->wait_in_kernel = false;
+        op->fpush.active = false;
         RDYB_CALL(rc);
         op->cur ^= 1;
-        if (s + 1 < nsteps) RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+        if (fused) ++op->p2p_epoch; /* raised in the neighbours by the kernel itself */
+        else if (s + 1 < nsteps) RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
         continue;
       }
       RDYB_CALL(launch_cells(op, in, out, dt, true, 0, op->NI, 0));                       /* interior cells: no ghost needed */

@@ -62,10 +62,23 @@ struct FixedArgs {
   /* multi-GPU, peer-memory halo: tiles >= wait_tile (the frontier tiles, numbered after the interior ones) stage ghost cells, so
    * the producer warp of a CTA waits until every neighbour's counter has reached wait_epoch before it issues the first of them;
    * interior and frontier then run in one launch.  wait_tile = INT32_MAX: no wait. */
-  int32_t wait_tile = 0x7fffffff, wait_peers = 0;
+  int32_t wait_tile = 0x7fffffff, wait_tile_end = 0x7fffffff, wait_peers = 0; /* launch positions [wait_tile, wait_tile_end) */
   unsigned int wait_epoch = 0;
   const unsigned int *wait_flags = nullptr;
   int *wait_status = nullptr;
+  /* fused halo push (Euler step only): when a frontier tile is done, its border cells are stored straight into the neighbours'
+   * ghost slots of the buffer this step writes; the CTA that finishes the last frontier tile of the launch raises this rank's
+   * counter in every neighbour.  Frontier tiles are then scheduled FIRST (tile_order), so the transfer overlaps the interior
+   * tiles and a step is one launch.  Send list of tile t: entries [push_range[t].x, + push_range[t].y). */
+  const int2 *push_range = nullptr;
+  const int32_t *push_src = nullptr;    /* [entries] device cell whose new state is sent */
+  double *const *push_dst = nullptr;    /* [entries] the neighbour's ghost slot (component 0) in the buffer this step writes */
+  const int32_t *push_rs = nullptr;     /* [entries] the neighbour's leading dimension */
+  unsigned int *push_counter = nullptr; /* tiles with sends finished so far, over all launches */
+  unsigned int push_target = 0;         /* value of *push_counter when this launch's last one is done */
+  unsigned int push_epoch = 0;
+  unsigned int *push_flag[RDYB_MAX_PEERS] = {};
+  int32_t push_peers = 0;
 };
 
 template <int NCONS>
@@ -114,7 +127,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
     bool waited = false;
     for (int it = 0; tile < q.tile_end; tile += G, ++it) {
       const int s = it % NS;
-      if (tile >= q.wait_tile && !waited) { /* halo_wait_kernel, inside the step (swe_kernels.cuh) */
+      if (tile >= q.wait_tile && tile < q.wait_tile_end && !waited) { /* halo_wait_kernel, inside the step (swe_kernels.cuh) */
         if (lane < q.wait_peers) {
           const volatile unsigned int *f = q.wait_flags + lane;
           const long long t0 = clock64();
@@ -320,6 +333,29 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       if (EULER) { a.o0[i] = h + dt * F0; a.o1[i] = hu + dt * F1; a.o2[i] = hv + dt * F2; }
       else { a.o0[i] = F0; a.o1[i] = F1; a.o2[i] = F2; }
     }
+    if (EULER && q.push_src && tile < q.wait_tile_end) { /* fused halo push of a frontier tile's border cells (uniform per CTA; frontier tiles come first) */
+      const int tn = p.tile_order ? __ldg(p.tile_order + tile) : tile;
+      const int2 sd = __ldg(q.push_range + tn);
+      if (sd.y > 0) {
+        fixed_consumer_sync<NCONS>(); /* every cell of the tile has been written */
+        for (int k = tid; k < sd.y; k += NCONS) {
+          const int c = q.push_src[sd.x + k];
+          double *d = q.push_dst[sd.x + k];
+          const int64_t rs = q.push_rs[sd.x + k];
+          d[0] = __ldcg(a.o0 + c); d[rs] = __ldcg(a.o1 + c); d[2 * rs] = __ldcg(a.o2 + c);
+        }
+        __threadfence_system(); /* the peer stores above before the counters below */
+        fixed_consumer_sync<NCONS>();
+        if (tid == 0) {
+          const unsigned int done = atomicAdd(q.push_counter, 1u) + 1u;
+          if (done == q.push_target) { /* the last tile with sends of this launch: every other CTA fenced before its atomicAdd */
+            __threadfence_system();
+            for (int pp = 0; pp < q.push_peers; ++pp) *reinterpret_cast<volatile unsigned int *>(q.push_flag[pp]) = q.push_epoch;
+            __threadfence_system();
+          }
+        }
+      }
+    }
     mbar_arrive(&S.empty_bar[s]); /* this thread is done reading stage s */
   }
 
@@ -400,6 +436,15 @@ struct FixedWait {
   unsigned int epoch;
   const unsigned int *flags;
   int *status;
+  /* fused push (optional): see FixedArgs */
+  const int32_t *order = nullptr; /* launch order with the frontier tiles first */
+  const int2 *push_range = nullptr;
+  const int32_t *push_src = nullptr;
+  double *const *push_dst = nullptr;
+  const int32_t *push_rs = nullptr;
+  unsigned int *push_counter = nullptr;
+  unsigned int push_target = 0, push_epoch = 0;
+  unsigned int *const *push_flag = nullptr;
 };
 
 static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a, int32_t n_interior,
@@ -418,7 +463,15 @@ static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T
   if (d.order) { if (d.sub_begin > q.tile_begin) q.tile_begin = d.sub_begin; if (d.sub_end < q.tile_end) q.tile_end = d.sub_end; }
   if (q.tile_end <= q.tile_begin) return RDYB_SUCCESS;
   if (wait && wait->peers > 0 && !d.order && q.tile_end > T.num_interior_tiles) {
-    q.wait_tile = T.num_interior_tiles; q.wait_peers = wait->peers; q.wait_epoch = wait->epoch; q.wait_flags = wait->flags; q.wait_status = wait->status;
+    q.wait_tile = T.num_interior_tiles; q.wait_tile_end = T.num_tiles;
+    q.wait_peers = wait->peers; q.wait_epoch = wait->epoch; q.wait_flags = wait->flags; q.wait_status = wait->status;
+    if (wait->push_src && euler && q.tile_begin == 0 && q.tile_end == T.num_tiles) { /* whole range, frontier tiles first */
+      p.tile_order = wait->order;
+      q.wait_tile = 0; q.wait_tile_end = T.num_tiles - T.num_interior_tiles;
+      q.push_range = wait->push_range; q.push_src = wait->push_src; q.push_dst = wait->push_dst; q.push_rs = wait->push_rs; q.push_counter = wait->push_counter;
+      q.push_target = wait->push_target; q.push_epoch = wait->push_epoch; q.push_peers = wait->peers;
+      for (int pp = 0; pp < wait->peers && pp < RDYB_MAX_PEERS; ++pp) q.push_flag[pp] = wait->push_flag[pp];
+    }
   }
   const bool hr = cfg.well_balancing == RDYB_WELL_BALANCING_HR;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
