@@ -8,6 +8,7 @@
 #include "device_layout.h"
 
 #include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -335,9 +336,138 @@ static int edges_reserve(RdybTiledLayout *T, int64_t *cap, int64_t need) {
   return RDYB_SUCCESS;
 }
 
+/* ---- bank-aware order of a tile's edges ----
+ * K4 reads shared memory through two kinds of gathers: phase 2 loads the staged state of an edge's left and right cell
+ * (index = tile-local cell), phase 3 loads the flux of each of a cell's edges (index = edge slot).  A 64-bit shared load is
+ * served per half-warp, one wavefront per distinct 8-byte word and bank pair, so 16 consecutive threads whose indices
+ * collide modulo 16 are replayed: with the edges in cell-major order a gather costs 3.8 (right cells) to 4.3 (fluxes)
+ * wavefronts per warp instead of 2 (scratch/bank/bankmodel.c reproduces the ncu counters: 3.9 and 4 - 4.7).  The order of a
+ * tile's edges is free (each cell keeps ITS edges in the reference's accumulation order, so results are bit-identical), so
+ * it is chosen here: slot = 16 * group + lane with
+ *   - the LANE (slot mod 16) of the edges gathered together by 16 consecutive cells in phase 3 pairwise distinct (a greedy
+ *     edge colouring: an edge belongs to at most two such sets, its left and its right cell's), and
+ *   - within a GROUP (the 16 edges of one half-warp in phase 2) left cells, and right cells, in distinct bank pairs
+ *     (assignment lane by lane, cheapest free group first, then pairwise swaps).
+ * Modelled wavefronts per warp instruction on the floodplain mesh: left cells 2.69 -> 3.12, right cells 3.81 -> 3.16, fluxes
+ * 4.30 -> 2.60, i.e. 18 % fewer gather wavefronts per tile.  MEASURED on the B200 (A/B, same box, 300 steps, twice each):
+ * 0.3364 / 0.3363 ms with, 0.3400 / 0.3364 ms without -- no difference, so bank conflicts are not what limits K4 and the pass
+ * (0.4 ms of host time per tile) is OFF unless RDYB_EDGE_SCHEDULE is set. */
+#define ES_MAX_EDGES 2048
+#define ES_MAX_GROUPS (ES_MAX_EDGES / 16)
+/* perm[old slot] = new slot; returns 0 when the tile is left as it is */
+static int tile_edge_schedule(int32_t ne, const uint32_t *lr, int32_t ncell, int32_t W, const uint16_t *cell_edges, size_t S, int32_t cb, int32_t *perm) {
+  if (ne < 32 || ne > ES_MAX_EDGES) return 0;
+  const int32_t G = (ne + 15) / 16, rem = ne - 16 * (G - 1), CG = (ncell + 15) / 16, nsets = W * CG;
+  int32_t (*eset)[2] = malloc(sizeof(int32_t[2]) * (size_t)ne);
+  uint8_t *nset = calloc((size_t)ne, 1);
+  uint8_t (*setcnt)[16] = calloc((size_t)nsets, 16);
+  if (!eset || !nset || !setcnt) { free(eset); free(nset); free(setcnt); return 0; }
+  uint8_t lane[ES_MAX_EDGES];
+  int16_t order[ES_MAX_EDGES], grp[ES_MAX_EDGES];
+  int ok = 1;
+  for (int32_t k = 0; k < W; ++k)
+    for (int32_t t = 0; t < ncell; ++t) {
+      const uint16_t ce = cell_edges[(size_t)k * S + cb + t];
+      if (ce == 0xffffu) continue;
+      const int32_t e = ce & 0x7fff;
+      if (e < ne && nset[e] < 2 && !(nset[e] == 1 && eset[e][0] == k * CG + t / 16)) eset[e][nset[e]++] = k * CG + t / 16; /* both cells in one set: a broadcast */
+    }
+#define LCOST(e, c) ((nset[e] > 0 ? setcnt[eset[e][0]][c] : 0) + (nset[e] > 1 ? setcnt[eset[e][1]][c] : 0))
+#define LADD(e, c, d) do { if (nset[e] > 0) setcnt[eset[e][0]][c] += (d); if (nset[e] > 1) setcnt[eset[e][1]][c] += (d); } while (0)
+  /* ---- lanes: most constrained edges first, the free-est lane on ties ---- */
+  int32_t no = 0, cap[16];
+  for (int pass = 2; pass >= 0; --pass)
+    for (int32_t e = 0; e < ne; ++e) if (nset[e] == pass) order[no++] = (int16_t)e;
+  for (int c = 0; c < 16; ++c) cap[c] = c < rem ? G : G - 1;
+  for (int32_t i = 0; i < ne; ++i) {
+    const int32_t e = order[i];
+    int best = -1, bcost = 0, bcap = 0;
+    for (int c = 0; c < 16; ++c) {
+      if (!cap[c]) continue;
+      const int cost = LCOST(e, c);
+      if (best < 0 || cost < bcost || (cost == bcost && cap[c] > bcap)) { best = c; bcost = cost; bcap = cap[c]; }
+    }
+    lane[e] = (uint8_t)best; cap[best]--;
+    LADD(e, best, 1);
+  }
+  /* repair: an edge whose lane collides trades lanes with any edge when the two together collide less afterwards */
+  for (int sweep = 0; sweep < 3; ++sweep) {
+    int changed = 0;
+    for (int32_t e = 0; e < ne; ++e) {
+      int ce_ = LCOST(e, lane[e]) - nset[e];
+      if (ce_ <= 0) continue;
+      for (int32_t f = 0; f < ne && ce_ > 0; ++f) {
+        const int a = lane[e], b = lane[f];
+        if (b == a || LCOST(e, b) >= ce_) continue; /* e would not be better off in f's lane */
+        const int before = ce_ + LCOST(f, b) - nset[f];
+        LADD(e, a, -1); LADD(f, b, -1);
+        const int after = LCOST(e, b) + LCOST(f, a);
+        if (after < before) { lane[e] = (uint8_t)b; lane[f] = (uint8_t)a; LADD(e, b, 1); LADD(f, a, 1); changed = 1; ce_ = LCOST(e, b) - nset[e]; }
+        else { LADD(e, a, 1); LADD(f, b, 1); }
+      }
+    }
+    if (!changed) break;
+  }
+#undef LCOST
+#undef LADD
+  /* ---- groups, lane by lane: each lane has exactly one edge in each of its groups ---- */
+  uint8_t cl[ES_MAX_GROUPS][16], cr[ES_MAX_GROUPS][16];
+  uint16_t fl[ES_MAX_GROUPS][16], fr[ES_MAX_GROUPS][16]; /* the first cell in each bank pair: the same cell again is a broadcast, not a conflict */
+  memset(cl, 0, sizeof(cl[0]) * (size_t)G); memset(cr, 0, sizeof(cr[0]) * (size_t)G);
+#define EL(e) (lr[e] & 0xffffu)
+#define ER(e) (lr[e] >> 16)
+#define SIDE(cnt, first, g, x) ((cnt)[g][(x) & 15u] == 0 || ((cnt)[g][(x) & 15u] == 1 && (first)[g][(x) & 15u] == (x)) ? 0 : (cnt)[g][(x) & 15u])
+#define GCOST(e, g) (SIDE(cl, fl, g, EL(e)) + (ER(e) == 0xffffu ? 0 : SIDE(cr, fr, g, ER(e))))
+#define GADD(cnt, first, g, x) do { uint8_t *c_ = &(cnt)[g][(x) & 15u]; if (*c_ == 0) { (first)[g][(x) & 15u] = (uint16_t)(x); *c_ = 1; } else if (!(*c_ == 1 && (first)[g][(x) & 15u] == (x))) ++*c_; } while (0)
+  for (int c = 0; c < 16 && ok; ++c) {
+    const int32_t ng = c < rem ? G : G - 1;
+    int16_t members[ES_MAX_GROUPS];
+    uint8_t gfree[ES_MAX_GROUPS];
+    int32_t nm = 0;
+    for (int32_t e = 0; e < ne; ++e) if (lane[e] == c) { if (nm < ES_MAX_GROUPS) members[nm] = (int16_t)e; nm++; }
+    if (nm != ng) { ok = 0; break; }
+    memset(gfree, 1, (size_t)ng);
+    for (int32_t i = 0; i < nm; ++i) {
+      const int32_t e = members[i];
+      int32_t bg = -1, bc = 0;
+      for (int32_t g = 0; g < ng; ++g) {
+        if (!gfree[g]) continue;
+        const int cst = GCOST(e, g);
+        if (bg < 0 || cst < bc) { bg = g; bc = cst; if (!cst) break; }
+      }
+      grp[e] = (int16_t)bg; gfree[bg] = 0;
+    }
+    for (int sweep = 0; sweep < 2; ++sweep)
+      for (int32_t i = 0; i < nm; ++i) {
+        const int32_t e = members[i];
+        if (!GCOST(e, grp[e])) continue;
+        for (int32_t j = 0; j < nm; ++j) {
+          const int32_t f = members[j];
+          if (GCOST(e, grp[f]) + GCOST(f, grp[e]) < GCOST(e, grp[e]) + GCOST(f, grp[f])) { const int16_t x = grp[e]; grp[e] = grp[f]; grp[f] = x; if (!GCOST(e, grp[e])) break; }
+        }
+      }
+    for (int32_t i = 0; i < nm; ++i) {
+      const int32_t e = members[i];
+      GADD(cl, fl, grp[e], EL(e));
+      if (ER(e) != 0xffffu) GADD(cr, fr, grp[e], ER(e));
+      perm[e] = 16 * grp[e] + c;
+    }
+  }
+#undef GCOST
+#undef GADD
+#undef SIDE
+#undef EL
+#undef ER
+  free(eset); free(nset); free(setcnt);
+  return ok;
+}
+
 int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLayout *T) {
   int ierr = RDYB_SUCCESS;
   int32_t *tmp_halo = NULL, *slot_edge = NULL;
+  int32_t eperm[ES_MAX_EDGES];
+  double escratch[ES_MAX_EDGES];
+  const int schedule = getenv("RDYB_EDGE_SCHEDULE") != NULL; /* opt-in: measured, no gain */
   RDYB_CHECK(L && T, RDYB_ERR_ARG, "tiled layout: NULL argument");
   RDYB_CHECK(tile_cells >= 128 && tile_cells <= 8192 && tile_cells % 8 == 0, RDYB_ERR_ARG, "tiled layout: tile_cells (%d) must be a multiple of 8 in [128, 8192]", tile_cells);
   memset(T, 0, sizeof(*T));
@@ -432,6 +562,23 @@ int rdyb_tiled_layout_build(const RdybLayout *L, int32_t tile_cells, RdybTiledLa
         }
         T->cell_edges[q] = (uint16_t)((uint32_t)e | (me_left ? 0u : 0x8000u));
       }
+    /* pass 3: bank-aware edge order (see tile_edge_schedule) */
+    if (schedule && nte <= ES_MAX_EDGES && tile_edge_schedule(nte, T->edge_lr + ne, ncell, W, T->cell_edges, S, cb, eperm)) {
+#define PERMUTE(field, type)                                                              \
+      do {                                                                                \
+        type *a_ = T->field + ne, *b_ = (type *)escratch;                                  \
+        for (int32_t e = 0; e < nte; ++e) b_[eperm[e]] = a_[e];                           \
+        memcpy(a_, b_, sizeof(type) * (size_t)nte);                                       \
+      } while (0)
+      PERMUTE(edge_lr, uint32_t); PERMUTE(edge_bidx, int32_t); PERMUTE(edge_id, int32_t); PERMUTE(edge_cell, int32_t);
+      PERMUTE(edge_sn, double); PERMUTE(edge_cn, double); PERMUTE(edge_len, double);
+#undef PERMUTE
+      for (int32_t k = 0; k < W; ++k)
+        for (int32_t i = cb; i < ce; ++i) {
+          const uint16_t v = T->cell_edges[(size_t)k * S + i];
+          if (v != 0xffffu) T->cell_edges[(size_t)k * S + i] = (uint16_t)((uint32_t)eperm[v & 0x7fffu] | (v & 0x8000u));
+        }
+    }
     { int32_t *d = &T->tile_desc[8 * (size_t)t]; d[0] = cb; d[1] = ncell; d[2] = (int32_t)ne; d[3] = nte; d[4] = (int32_t)nh; d[5] = nth; d[6] = 0; d[7] = 0; }
     nh += nth; ne += nte;
     if (nth > T->max_halo) T->max_halo = nth;
