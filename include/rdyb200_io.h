@@ -48,6 +48,32 @@ int rdyb_petsc_vec_read(const char *path, int64_t *n, double **values, int32_t *
 int rdyb_petsc_vec_write(const char *path, int64_t n, const double *values, int32_t index_bytes);
 void rdyb_free(void *p);
 
+/* ---- checkpoints (binary format): WriteCheckpointFile / ReadCheckpointFile, src/checkpoint.c:153-212, 258-320 ----
+ * A checkpoint is a PETSc binary stream of two records: the PetscBag "metadata" {nproc, t, dt, step} (CreateMetadata, :57-76) and
+ * the solution Vec in NATURAL cell order, block size = number of components (DMPlexGlobalToNatural + VecView, :190-205), next to a
+ * "<file>.info" holding "-vecload_block_size <ndof>" as the binary viewer leaves it.  No PETSc here: the bag record follows
+ * PetscBagView's binary layout (PETSc 3.24 src/sys/classes/bag/bag.c: classid 1211219, a deprecated size word, the item count,
+ * name[64], help[128], then per item {offset, PetscDataType, name[64], help[128], msize, value}).  The reference tree holds no
+ * checkpoint file to pin the bag bytes against ("parity unpinned" for the bag; the Vec record is the format of the share/
+ * fixtures, which is pinned) and the item offsets are build-specific in PETSc (PetscBagLoad does not use them). */
+typedef struct {
+  int32_t nproc; /* number of MPI tasks that wrote the file */
+  double t, dt;  /* simulation time and time step, in seconds */
+  int32_t step;
+} RdybCheckpointMetadata;
+
+/* "<directory>/<prefix>.rdycore.r.<index, zero-padded to the digits of max_index>" (GenerateE3SMCheckpointFilenameBase, :141-152);
+ * the binary format appends ".bin" */
+int rdyb_checkpoint_filename_base(const char *directory, const char *prefix, int64_t index, int64_t max_index, char *out, int32_t capacity);
+/* Each caller writes the rows natural_ids[i] (NULL: rows 0..n_local-1) of the natural-order solution: values[ndof * i + c].  One
+ * process per GPU calls it with its owned cells and their global ids: the rows land at their natural offsets with pwrite, so no
+ * gather to rank 0 is needed; the call with write_header != 0 (rank 0) also writes the two record headers and the .info file.
+ * index_bytes = 4 or 8 (the PetscInt of the build that is to read the file). */
+int rdyb_checkpoint_write(const char *path, const RdybCheckpointMetadata *metadata, int64_t num_global_cells, int32_t ndof, int32_t index_bytes,
+                          int64_t n_local, const int64_t *natural_ids, const double *values, int32_t write_header);
+/* *values (malloc'ed, rdyb_free) receives the natural-order solution, *n_values its length (cells * ndof) */
+int rdyb_checkpoint_read(const char *path, RdybCheckpointMetadata *metadata, int64_t *n_values, double **values, int32_t *index_bytes);
+
 #ifdef __cplusplus
 }
 #endif

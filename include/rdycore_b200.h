@@ -97,6 +97,12 @@ PetscErrorCode RDyB200SetDevice(RDy rdy, int device);
 PetscErrorCode RDyB200SetKernel(RDy rdy, PetscInt kind, PetscInt tile_cells);
 /* the operator behind the RDy (valid after RDySetup): for halo setup, diagnostics, device pointers */
 PetscErrorCode RDyB200GetOperator(RDy rdy, RdybOperator *op);
+/* Checkpoints, binary format (include/rdyb200_io.h).  Write: WriteCheckpointFile (src/checkpoint.c:153-212) to "<filename_base>.bin" —
+ * metadata {nproc, t, dt, step} and the solution in natural (global cell id) order; on a partitioned mesh every process calls it with its
+ * rank and the global cell count, and writes its owned rows in place (rank 0 also writes the headers).  Read: ReadCheckpointFile +
+ * ConsumeMetadata (:80-97, 258-320): state, dt and — unless `reinitialize`, the deck's restart.reinitialize — time and step. */
+PetscErrorCode RDyB200WriteCheckpoint(RDy rdy, const char *filename_base, PetscInt nproc, PetscInt rank, PetscInt num_global_cells);
+PetscErrorCode RDyB200ReadCheckpoint(RDy rdy, const char *filename, PetscBool reinitialize);
 /* max Courant number of the last right-hand-side evaluation (GetOperatorDiagnostics, src/operator.c:889-893) */
 PetscErrorCode RDyB200GetMaxCourantNumber(RDy rdy, PetscReal *courant);
 

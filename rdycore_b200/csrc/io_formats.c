@@ -2,11 +2,14 @@
  * See include/rdyb200_io.h for what each entry point replaces in the reference.  Written against the published file formats
  * (NetCDF classic format specification; PETSc binary viewer: big-endian {VEC_FILE_CLASSID, n, n doubles}); the reference itself
  * reaches them through libexodus/libnetcdf and PETSc, none of which exist here. */
+#define _XOPEN_SOURCE 700 /* pwrite, ftruncate */
 #include "rdyb200_io.h"
 
+#include <fcntl.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
 #include "rdyb_error.h"
 
@@ -358,4 +361,164 @@ int rdyb_exodus_read(const char *path, RdybExodusMesh *mesh) {
   free(b);
   if (rc) rdyb_exodus_free(mesh);
   return rc;
+}
+
+/* ---------------- checkpoints: PetscBag "metadata" + natural-order Vec (src/checkpoint.c) ---------------- */
+#define RDYB_BAG_FILE_CLASSID 1211219
+#define RDYB_BAG_NAME_LENGTH 64
+#define RDYB_BAG_HELP_LENGTH 128
+enum { RDYB_PETSC_DOUBLE = 1, RDYB_PETSC_INT = 16 }; /* PetscDataType */
+/* what an item offset would be in a 64-bit PETSc build: the bag header rounded up to a PetscScalar, then the field's offset in
+ * CheckpointMetadata (src/checkpoint.c:49-54).  Informational: PetscBagLoad walks the registered items, not these numbers. */
+#define RDYB_BAG_HEADER_BYTES 248
+
+int rdyb_checkpoint_filename_base(const char *directory, const char *prefix, int64_t index, int64_t max_index, char *out, int32_t capacity) {
+  RDYB_CHECK(directory && prefix && out && capacity > 0, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(index >= 0 && max_index >= 1, RDYB_ERR_ARG, "checkpoint index %lld of %lld", (long long)index, (long long)max_index);
+  int digits = 1;
+  for (int64_t v = max_index; v >= 10; v /= 10) ++digits;
+  const int n = snprintf(out, (size_t)capacity, "%s/%s.rdycore.r.%0*lld", directory, prefix, digits, (long long)index);
+  RDYB_CHECK(n > 0 && n < capacity, RDYB_ERR_ARG_SIZ, "checkpoint file name does not fit %d bytes", capacity);
+  return RDYB_SUCCESS;
+}
+
+static size_t put_int(unsigned char *p, int64_t v, int index_bytes) {
+  for (int j = 0; j < index_bytes; ++j) p[j] = (unsigned char)((uint64_t)v >> (8 * (index_bytes - 1 - j)));
+  return (size_t)index_bytes;
+}
+static size_t put_f64(unsigned char *p, double d) {
+  uint64_t u;
+  memcpy(&u, &d, 8);
+  for (int j = 0; j < 8; ++j) p[j] = (unsigned char)(u >> (8 * (7 - j)));
+  return 8;
+}
+static size_t put_str(unsigned char *p, const char *s, size_t field) {
+  memset(p, 0, field);
+  strncpy((char *)p, s, field - 1);
+  return field;
+}
+static size_t bag_item_header(unsigned char *p, int64_t offset, int dtype, const char *name, const char *help, int index_bytes) {
+  size_t k = 0;
+  k += put_int(p + k, RDYB_BAG_HEADER_BYTES + offset, index_bytes);
+  k += put_int(p + k, dtype, index_bytes);
+  k += put_str(p + k, name, RDYB_BAG_NAME_LENGTH);
+  k += put_str(p + k, help, RDYB_BAG_HELP_LENGTH);
+  k += put_int(p + k, 1, index_bytes); /* msize: one entry */
+  return k;
+}
+/* bytes of the bag record: 3 ints + name + help, then 4 items of {3 ints + name + help + value} */
+static size_t bag_bytes(int index_bytes) {
+  const size_t item = 3 * (size_t)index_bytes + RDYB_BAG_NAME_LENGTH + RDYB_BAG_HELP_LENGTH;
+  return item + 4 * item + 2 * (size_t)index_bytes + 2 * 8;
+}
+
+int rdyb_checkpoint_write(const char *path, const RdybCheckpointMetadata *md, int64_t num_global_cells, int32_t ndof, int32_t index_bytes,
+                          int64_t n_local, const int64_t *natural_ids, const double *values, int32_t write_header) {
+  RDYB_CHECK(path && (values || n_local == 0), RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(index_bytes == 4 || index_bytes == 8, RDYB_ERR_ARG, "index_bytes must be 4 or 8");
+  RDYB_CHECK(num_global_cells >= 0 && ndof >= 1 && n_local >= 0 && n_local <= num_global_cells, RDYB_ERR_ARG, "bad sizes");
+  RDYB_CHECK(!write_header || md, RDYB_ERR_ARG, "the header needs the metadata");
+  const size_t bag = bag_bytes(index_bytes), data0 = bag + 2 * (size_t)index_bytes;
+  const int fd = open(path, O_WRONLY | O_CREAT, 0644);
+  RDYB_CHECK(fd >= 0, RDYB_ERR_USER, "Cannot open file %s for writing", path);
+  int ok = 1;
+  if (write_header) {
+    unsigned char *h = (unsigned char *)malloc(data0);
+    if (!h) { close(fd); return rdyb_fail(RDYB_ERR_MEM, "out of memory"); }
+    size_t k = 0;
+    k += put_int(h + k, RDYB_BAG_FILE_CLASSID, index_bytes);
+    k += put_int(h + k, 0, index_bytes); /* deprecated bag size */
+    k += put_int(h + k, 4, index_bytes); /* items */
+    k += put_str(h + k, "metadata", RDYB_BAG_NAME_LENGTH);
+    k += put_str(h + k, "Checkpoint metadata", RDYB_BAG_HELP_LENGTH);
+    /* field offsets in {PetscInt nproc; PetscReal t; PetscReal dt; PetscInt step;}: 0, 8, 16, 24 for either PetscInt size */
+    k += bag_item_header(h + k, 0, RDYB_PETSC_INT, "nproc", "Number of MPI tasks", index_bytes);
+    k += put_int(h + k, md->nproc, index_bytes);
+    k += bag_item_header(h + k, 8, RDYB_PETSC_DOUBLE, "t", "Simulation time", index_bytes);
+    k += put_f64(h + k, md->t);
+    k += bag_item_header(h + k, 16, RDYB_PETSC_DOUBLE, "dt", "Simulation timestep", index_bytes);
+    k += put_f64(h + k, md->dt);
+    k += bag_item_header(h + k, 24, RDYB_PETSC_INT, "step", "Simulation step number", index_bytes);
+    k += put_int(h + k, md->step, index_bytes);
+    k += put_int(h + k, RDYB_VEC_FILE_CLASSID, index_bytes);
+    k += put_int(h + k, num_global_cells * ndof, index_bytes);
+    ok = k == data0 && pwrite(fd, h, data0, 0) == (ssize_t)data0 && ftruncate(fd, (off_t)(data0 + 8 * (size_t)(num_global_cells * ndof))) == 0;
+    free(h);
+    if (ok) { /* the viewer's .info file: the block size VecLoad picks up */
+      char info[4096];
+      if (snprintf(info, sizeof info, "%s.info", path) < (int)sizeof info) {
+        FILE *f = fopen(info, "w");
+        if (f) { fprintf(f, "-vecload_block_size %d\n", ndof); fclose(f); }
+      }
+    }
+  }
+  /* rows: runs of consecutive natural ids go out in one pwrite */
+  const size_t row = 8 * (size_t)ndof, cap = 4096;
+  unsigned char *buf = (unsigned char *)malloc(cap * row);
+  if (!buf) { close(fd); return rdyb_fail(RDYB_ERR_MEM, "out of memory"); }
+  for (int64_t i = 0; ok && i < n_local;) {
+    const int64_t id0 = natural_ids ? natural_ids[i] : i;
+    if (id0 < 0 || id0 >= num_global_cells) { ok = 0; rdyb_fail(RDYB_ERR_USER, "natural cell id %lld out of range", (long long)id0); free(buf); close(fd); return RDYB_ERR_USER; }
+    int64_t j = i + 1;
+    while (j < n_local && (size_t)(j - i) < cap && (natural_ids ? natural_ids[j] : j) == id0 + (j - i)) ++j;
+    for (int64_t r = i; r < j; ++r)
+      for (int c = 0; c < ndof; ++c) put_f64(buf + (size_t)(r - i) * row + 8 * (size_t)c, values[(size_t)r * ndof + c]);
+    const size_t nb = (size_t)(j - i) * row;
+    ok = pwrite(fd, buf, nb, (off_t)(data0 + (size_t)id0 * row)) == (ssize_t)nb;
+    i = j;
+  }
+  free(buf);
+  ok = close(fd) == 0 && ok;
+  RDYB_CHECK(ok, RDYB_ERR_USER, "Short write to %s", path);
+  return RDYB_SUCCESS;
+}
+
+int rdyb_checkpoint_read(const char *path, RdybCheckpointMetadata *md, int64_t *n_values, double **values, int32_t *index_bytes) {
+  RDYB_CHECK(path && md && n_values && values, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(strstr(path, ".bin"), RDYB_ERR_USER, "Invalid checkpoint file: %s", path); /* src/checkpoint.c:271-280; .h5 is not read here */
+  unsigned char *b = NULL;
+  size_t len = 0;
+  RDYB_CALL(slurp(path, &b, &len));
+  int ib = 0;
+  if (len >= 8 && be32(b) == RDYB_BAG_FILE_CLASSID) ib = 4;
+  else if (len >= 16 && be64(b) == RDYB_BAG_FILE_CLASSID) ib = 8;
+#define GET_INT(at) (ib == 4 ? (int64_t)(int32_t)be32(b + (at)) : (int64_t)be64(b + (at)))
+  int ierr = RDYB_SUCCESS;
+  if (!ib || len < bag_bytes(ib) + 2 * (size_t)ib || GET_INT(2 * (size_t)ib) != 4) ierr = rdyb_fail(RDYB_ERR_USER, "%s does not start with the checkpoint metadata bag", path);
+  if (!ierr) {
+    const size_t item = 3 * (size_t)ib + RDYB_BAG_NAME_LENGTH + RDYB_BAG_HELP_LENGTH;
+    static const char *names[4] = {"nproc", "t", "dt", "step"};
+    size_t k = item;
+    for (int i = 0; i < 4 && !ierr; ++i) { /* the items in the order CreateMetadata registers them */
+      const int64_t dtype = GET_INT(k + (size_t)ib), msize = GET_INT(k + 2 * (size_t)ib + RDYB_BAG_NAME_LENGTH + RDYB_BAG_HELP_LENGTH);
+      const int is_int = i == 0 || i == 3;
+      if (strncmp((const char *)b + k + 2 * (size_t)ib, names[i], RDYB_BAG_NAME_LENGTH) != 0 || msize != 1 || dtype != (is_int ? RDYB_PETSC_INT : RDYB_PETSC_DOUBLE)) {
+        ierr = rdyb_fail(RDYB_ERR_USER, "%s: metadata item %d is not '%s'", path, i, names[i]);
+        break;
+      }
+      k += item;
+      if (i == 0) md->nproc = (int32_t)GET_INT(k);
+      else if (i == 1) md->t = bef64(b + k);
+      else if (i == 2) md->dt = bef64(b + k);
+      else md->step = (int32_t)GET_INT(k);
+      k += is_int ? (size_t)ib : 8;
+    }
+    if (!ierr) {
+      const int64_t count = GET_INT(k) == RDYB_VEC_FILE_CLASSID ? GET_INT(k + (size_t)ib) : -1;
+      k += 2 * (size_t)ib;
+      if (count < 0 || k + 8 * (size_t)count > len) ierr = rdyb_fail(RDYB_ERR_USER, "%s: no solution Vec after the metadata, or truncated", path);
+      else {
+        double *v = (double *)malloc(8 * (size_t)(count > 0 ? count : 1));
+        if (!v) ierr = rdyb_fail(RDYB_ERR_MEM, "out of memory reading %s", path);
+        else {
+          for (int64_t i = 0; i < count; ++i) v[i] = bef64(b + k + 8 * (size_t)i);
+          *n_values = count; *values = v;
+          if (index_bytes) *index_bytes = ib;
+        }
+      }
+    }
+  }
+#undef GET_INT
+  free(b);
+  return ierr;
 }

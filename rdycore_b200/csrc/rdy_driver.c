@@ -15,6 +15,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "rdyb200_io.h"
 #include "rdyb_error.h"
 
 #define INVALID_REAL (-999.0) /* src/yaml_input.c: the "not given" markers */
@@ -438,6 +439,63 @@ PetscErrorCode RDyB200GetMaxCourantNumber(RDy rdy, PetscReal *courant) {
   RDYB_CALL(rdyb_operator_get_courant(rdy->op, &d));
   *courant = d.max_courant_num;
   return PETSC_SUCCESS;
+}
+
+/* ------------------------------------------------------------------ checkpoints (src/checkpoint.c) ---- */
+static int owned_natural_ids(RDy rdy, int64_t **ids) {
+  const void *g, *o2l;
+  int64_t     ng, no;
+  RDYB_CALL(rdyb_hostmesh_array(rdy->mesh, "cell_global_ids", &g, &ng));
+  RDYB_CALL(rdyb_hostmesh_array(rdy->mesh, "owned_to_local", &o2l, &no));
+  *ids = (int64_t *)malloc(sizeof(int64_t) * (size_t)(rdy->num_owned > 0 ? rdy->num_owned : 1));
+  RDYB_CHECK(*ids, RDYB_ERR_MEM, "out of memory");
+  for (int32_t i = 0; i < rdy->num_owned; ++i) (*ids)[i] = ((const int64_t *)g)[((const int32_t *)o2l)[i]];
+  return PETSC_SUCCESS;
+}
+
+PetscErrorCode RDyB200WriteCheckpoint(RDy rdy, const char *filename_base, PetscInt nproc, PetscInt rank, PetscInt num_global_cells) {
+  RDYB_CHECK(rdy && filename_base, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(rdy->is_setup, RDYB_ERR_USER, "RDySetup has not been called");
+  RDYB_CHECK(nproc >= 1 && rank >= 0 && rank < nproc && num_global_cells >= rdy->num_owned, RDYB_ERR_ARG, "bad partition description");
+  char path[4096]; /* PETSC_MAX_PATH_LEN */
+  RDYB_CHECK(snprintf(path, sizeof path, "%s.bin", filename_base) < (int)sizeof path, RDYB_ERR_ARG_SIZ, "file name too long");
+  double  *u   = (double *)malloc(sizeof(double) * 3 * (size_t)(rdy->num_owned > 0 ? rdy->num_owned : 1));
+  int64_t *ids = NULL;
+  RDYB_CHECK(u, RDYB_ERR_MEM, "out of memory");
+  int ierr = rdyb_operator_get_state(rdy->op, u);
+  if (!ierr) ierr = owned_natural_ids(rdy, &ids);
+  const RdybCheckpointMetadata md = {.nproc = nproc, .t = rdy->time, .dt = rdy->dt, .step = rdy->step};
+  if (!ierr) ierr = rdyb_checkpoint_write(path, &md, num_global_cells, 3, (int32_t)sizeof(PetscInt), rdy->num_owned, ids, u, rank == 0);
+  free(u);
+  free(ids);
+  return ierr;
+}
+
+PetscErrorCode RDyB200ReadCheckpoint(RDy rdy, const char *filename, PetscBool reinitialize) {
+  RDYB_CHECK(rdy && filename, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(rdy->is_setup, RDYB_ERR_USER, "RDySetup has not been called");
+  RdybCheckpointMetadata md;
+  int64_t                n = 0, *ids = NULL;
+  double                *nat = NULL;
+  RDYB_CALL(rdyb_checkpoint_read(filename, &md, &n, &nat, NULL));
+  int     ierr = owned_natural_ids(rdy, &ids);
+  double *u    = (double *)malloc(sizeof(double) * 3 * (size_t)(rdy->num_owned > 0 ? rdy->num_owned : 1));
+  if (!ierr && !u) ierr = rdyb_fail(RDYB_ERR_MEM, "out of memory");
+  for (int32_t i = 0; !ierr && i < rdy->num_owned; ++i) { /* DMPlexNaturalToGlobal: the rows of the owned cells */
+    if (ids[i] < 0 || 3 * ids[i] + 2 >= n) ierr = rdyb_fail(RDYB_ERR_ARG_SIZ, "checkpoint %s has %lld values; cell %lld is not in it", filename, (long long)n, (long long)ids[i]);
+    else memcpy(u + 3 * (size_t)i, nat + 3 * (size_t)ids[i], 3 * sizeof(double));
+  }
+  if (!ierr) ierr = rdyb_operator_set_state(rdy->op, u);
+  if (!ierr) { /* ConsumeMetadata */
+    rdy->dt = md.dt;
+    rdy->time = reinitialize ? 0.0 : md.t;
+    rdy->step = reinitialize ? 0 : md.step;
+    rdy->courant_valid = 0;
+  }
+  free(u);
+  free(ids);
+  rdyb_free(nat);
+  return ierr;
 }
 
 /* ------------------------------------------------------------------ time queries (src/rdyadvance.c:402-456) ---- */

@@ -66,6 +66,43 @@ def write_petsc_vec(path: str, values: np.ndarray, index_bytes: int = 4) -> None
     _lib.check(_lib.lib().rdyb_petsc_vec_write(str(path).encode(), C.c_int64(v.size), v.ctypes.data_as(C.POINTER(C.c_double)), C.c_int32(index_bytes)))
 
 
+class _CheckpointMetadata(C.Structure):
+    _fields_ = [("nproc", C.c_int32), ("t", C.c_double), ("dt", C.c_double), ("step", C.c_int32)]
+
+
+def checkpoint_filename_base(directory: str, prefix: str, index: int, max_index: int) -> str:
+    """GenerateE3SMCheckpointFilenameBase (src/checkpoint.c:141-152); the binary format appends '.bin'."""
+    buf = C.create_string_buffer(4096)
+    _lib.check(_lib.lib().rdyb_checkpoint_filename_base(directory.encode(), prefix.encode(), C.c_int64(index), C.c_int64(max_index), buf, C.c_int32(4096)))
+    return buf.value.decode()
+
+
+def write_checkpoint(path: str, values: np.ndarray, t: float, dt: float, step: int, nproc: int = 1, num_global_cells: int | None = None,
+                     natural_ids: np.ndarray | None = None, write_header: bool = True, index_bytes: int = 4) -> None:
+    """WriteCheckpointFile, binary format (src/checkpoint.c:153-212): values[(local cell), component] go to the rows natural_ids of the
+    natural-order solution (all rows when natural_ids is None); the rank with write_header writes the metadata bag and the Vec header."""
+    v = np.ascontiguousarray(values, dtype=np.float64)
+    assert v.ndim == 2
+    n, ndof = v.shape
+    ids = None if natural_ids is None else np.ascontiguousarray(natural_ids, dtype=np.int64)
+    md = _CheckpointMetadata(nproc, t, dt, step)
+    _lib.check(_lib.lib().rdyb_checkpoint_write(
+        str(path).encode(), C.byref(md), C.c_int64(n if num_global_cells is None else num_global_cells), C.c_int32(ndof), C.c_int32(index_bytes), C.c_int64(n),
+        None if ids is None else ids.ctypes.data_as(C.POINTER(C.c_int64)), v.ctypes.data_as(C.POINTER(C.c_double)), C.c_int32(1 if write_header else 0)))
+
+
+def read_checkpoint(path: str, ndof: int = 3) -> dict:
+    """ReadCheckpointFile, binary format (src/checkpoint.c:258-320): the metadata and the natural-order solution [cells, ndof]."""
+    lib = _lib.lib()
+    md, n, p, ib = _CheckpointMetadata(), C.c_int64(), C.POINTER(C.c_double)(), C.c_int32()
+    _lib.check(lib.rdyb_checkpoint_read(str(path).encode(), C.byref(md), C.byref(n), C.byref(p), C.byref(ib)))
+    try:
+        u = _arr(p, n.value, np.float64)
+    finally:
+        lib.rdyb_free(p)
+    return dict(nproc=md.nproc, t=md.t, dt=md.dt, step=md.step, index_bytes=ib.value, solution=u.reshape(-1, ndof))
+
+
 def mesh_from_exodus(ex: dict) -> HostMesh:
     return HostMesh.from_cells(ex["xyz"], ex["elem_offsets"], ex["elem_nodes"])
 

@@ -184,5 +184,15 @@ class RDy:
         check(lib().RDySetInitialConditions(self._h, vec.handle))
         vec.destroy()
 
+    def RDyB200WriteCheckpoint(self, filename_base: str, nproc: int = 1, rank: int = 0, num_global_cells: int | None = None) -> str:
+        """WriteCheckpointFile, binary format (src/checkpoint.c:153-212); returns the file name."""
+        n = self.RDyGetNumOwnedCells() if num_global_cells is None else num_global_cells
+        check(lib().RDyB200WriteCheckpoint(self._h, filename_base.encode(), C.c_int32(nproc), C.c_int32(rank), C.c_int32(n)))
+        return filename_base + ".bin"
+
+    def RDyB200ReadCheckpoint(self, filename: str, reinitialize: bool = False):
+        """ReadCheckpointFile (src/checkpoint.c:258-320): state, dt, and (unless reinitialize) time and step."""
+        check(lib().RDyB200ReadCheckpoint(self._h, filename.encode(), C.c_int(1 if reinitialize else 0)))
+
     def state(self) -> np.ndarray:
         return np.stack([self.RDyGetOwnedCellHeights(), self.RDyGetOwnedCellXMomenta(), self.RDyGetOwnedCellYMomenta()], axis=1)

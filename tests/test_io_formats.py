@@ -76,3 +76,65 @@ def test_mesh_and_boundaries_from_the_reference_meshes():
     bnd = io.boundaries_from_side_sets(mesh, ex)
     assert len(bnd) == 1 and len(bnd[0].edge_ids) == 20 == mesh.num_boundary_edges
     assert np.isclose(mesh.view_arrays()["cell_areas"][:100].sum(), 25.0)
+
+
+# ---- checkpoints (src/checkpoint.c, binary format) ----
+def test_checkpoint_file_names_follow_the_e3sm_pattern():
+    assert io.checkpoint_filename_base("checkpoints", "ex2b", 7, 1000) == "checkpoints/ex2b.rdycore.r.0007"
+    assert io.checkpoint_filename_base("checkpoints/member1", "run", 12, 99) == "checkpoints/member1/run.rdycore.r.12"
+    assert io.checkpoint_filename_base("d", "p", 0, 5) == "d/p.rdycore.r.0"
+
+
+@pytest.mark.parametrize("index_bytes", [4, 8])
+def test_checkpoint_round_trip_and_record_layout(tmp_path, index_bytes):
+    rng = np.random.default_rng(3)
+    u = rng.standard_normal((37, 3))
+    path = str(tmp_path / "run.rdycore.r.010.bin")
+    io.write_checkpoint(path, u, t=1.25, dt=0.005, step=250, nproc=4, index_bytes=index_bytes)
+    ck = io.read_checkpoint(path)
+    assert (ck["nproc"], ck["t"], ck["dt"], ck["step"], ck["index_bytes"]) == (4, 1.25, 0.005, 250, index_bytes)
+    assert np.array_equal(ck["solution"], u)
+    raw = open(path, "rb").read()
+    ib = index_bytes
+    geti = lambda at: int.from_bytes(raw[at:at + ib], "big", signed=True)
+    # PetscBagView: classid, deprecated size, item count, name[64], help[128]
+    assert geti(0) == 1211219 and geti(ib) == 0 and geti(2 * ib) == 4
+    assert raw[3 * ib:3 * ib + 64].rstrip(b"\0") == b"metadata" and raw[3 * ib + 64:3 * ib + 192].rstrip(b"\0") == b"Checkpoint metadata"
+    item = 3 * ib + 192
+    at = item
+    for name, dtype, width in (("nproc", 16, ib), ("t", 1, 8), ("dt", 1, 8), ("step", 16, ib)):
+        assert geti(at + ib) == dtype and raw[at + 2 * ib:at + 2 * ib + 64].rstrip(b"\0") == name.encode() and geti(at + 2 * ib + 192) == 1
+        at += item + width
+    # then the Vec record exactly as rdyb_petsc_vec_write lays it out: the tail of the file is a loadable PETSc Vec
+    assert geti(at) == 1211214 and geti(at + ib) == u.size
+    vec = str(tmp_path / "tail.bin")
+    open(vec, "wb").write(raw[at:])
+    assert np.array_equal(io.read_petsc_vec(vec), u.ravel())
+    assert open(path + ".info").read() == "-vecload_block_size 3\n"
+
+
+def test_checkpoint_written_by_parts_equals_the_serial_file(tmp_path):
+    """One process per GPU writes its owned rows at their natural offsets; the file is the serial one, in any order of the calls."""
+    rng = np.random.default_rng(4)
+    n = 1000
+    u = rng.standard_normal((n, 3))
+    serial, parts = str(tmp_path / "a.bin"), str(tmp_path / "b.bin")
+    io.write_checkpoint(serial, u, t=3.0, dt=0.1, step=30, nproc=3)
+    owner = rng.integers(0, 3, n)
+    open(parts, "wb").write(b"\xff" * 50000)  # a stale, longer file under the same name
+    for rank in (2, 0, 1):
+        ids = np.flatnonzero(owner == rank)
+        ids = ids[rng.permutation(ids.size)] if rank == 1 else ids  # one rank in a scrambled (device) order
+        io.write_checkpoint(parts, u[ids], t=3.0, dt=0.1, step=30, nproc=3, num_global_cells=n, natural_ids=ids, write_header=rank == 0)
+    assert open(parts, "rb").read() == open(serial, "rb").read()
+
+
+def test_checkpoint_errors(tmp_path):
+    with pytest.raises(RuntimeError, match="Invalid checkpoint file"):
+        io.read_checkpoint(str(tmp_path / "x.h5"))
+    p = str(tmp_path / "v.bin")
+    io.write_petsc_vec(p, np.arange(6.0))
+    with pytest.raises(RuntimeError, match="metadata bag"):
+        io.read_checkpoint(p)
+    with pytest.raises(RuntimeError, match="out of range"):
+        io.write_checkpoint(str(tmp_path / "w.bin"), np.zeros((2, 3)), 0.0, 1.0, 0, num_global_cells=2, natural_ids=np.array([0, 5]))

@@ -275,3 +275,43 @@ def test_setters_between_advances():
     with pytest.raises(RdybError):
         r.RDySetRegionalWaterSource(3, rain)
     r.RDyDestroy()
+
+
+@pytest.mark.gpu
+def test_restart_from_a_checkpoint_continues_bitwise(tmp_path):
+    """The reference's restart test: run, checkpoint, restart from the file in a fresh RDy, finish — identical to the uninterrupted run
+    (src/checkpoint.c:153-212, 258-320; GPU repeat runs are bitwise identical, so the comparison is exact)."""
+    from rdycore_b200 import io
+
+    case = cases.dam_break_quads(nx=50, ny=50, dt=1e-3)
+    straight = _make("dam_break.yaml", case)
+    while not straight.RDyFinished():
+        straight.RDyAdvance()
+    first = _make("dam_break.yaml", case)
+    first.RDyAdvance()
+    first.RDyAdvance()
+    base = io.checkpoint_filename_base(str(tmp_path), "dam_break", first.RDyGetStep(), 200)
+    assert base.endswith("dam_break.rdycore.r.100")
+    path = first.RDyB200WriteCheckpoint(base)
+    u_mid = first.state()
+    first.RDyDestroy()
+    ck = io.read_checkpoint(path)
+    assert (ck["nproc"], ck["step"]) == (1, 100) and ck["t"] == pytest.approx(0.1) and ck["dt"] == pytest.approx(1e-3)
+    assert np.array_equal(ck["solution"], u_mid)
+    second = _make("dam_break.yaml", case)
+    second.RDyB200ReadCheckpoint(path)
+    assert second.RDyGetStep() == 100 and second.RDyGetTime() == pytest.approx(0.1)
+    n_adv = 0
+    while not second.RDyFinished():
+        second.RDyAdvance()
+        n_adv += 1
+    assert n_adv == 2 and second.RDyGetStep() == 200
+    assert np.array_equal(second.state(), straight.state())
+    # restart.reinitialize: the state of the file, the clock back at zero
+    third = _make("dam_break.yaml", case)
+    third.RDyB200ReadCheckpoint(path, reinitialize=True)
+    assert third.RDyGetStep() == 0 and third.RDyGetTime() == 0.0 and np.array_equal(third.state(), u_mid)
+    with pytest.raises(RdybError, match="Invalid checkpoint file"):
+        third.RDyB200ReadCheckpoint(str(tmp_path / "nope.h5"))
+    for r in (straight, second, third):
+        r.RDyDestroy()
