@@ -40,7 +40,7 @@ def parse_args():
     p.add_argument("--nx", type=int, default=2236, help="quads per side of one GPU's block (cells = 2*nx*ny)")
     p.add_argument("--ny", type=int, default=0)
     p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed", "warp", "split"])
-    p.add_argument("--tile", type=int, default=int(os.environ.get("RDYB_TILE", "224")))
+    p.add_argument("--tile", type=int, default=None, help="cells per tile (default: RDYB_TILE, else 224 = K4's shape, 128 with --second-order = K2M's)")
     p.add_argument("--no-courant", action="store_true", help="skip the per-edge Courant diagnostic (the reference always computes it)")
     p.add_argument("--e2e-steps", type=int, default=10)
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
@@ -231,6 +231,8 @@ def run_b200_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     ny = args.ny or args.nx
+    if args.tile is None:
+        args.tile = int(os.environ.get("RDYB_TILE", "128" if args.second_order else "224"))
     px, py = block_grid(world)
     t_setup = time.perf_counter()
     if args.hr:
@@ -246,7 +248,8 @@ def run_b200_arm(args):
     kernel_name = {GATHER: "gather", TILED: "tiled", TILED_ASYNC: "tiled_async", TILED_FIXED: "tiled_fixed", WARP: "warp", TILED_SPLIT: "tiled_split"}[kernel]
     op.set_kernel(kernel, args.tile)
     if args.second_order:
-        kernel_name = "gather_muscl"  # the second-order path runs muscl_gradient_kernel + K1 whatever kernel is selected
+        # the second-order path runs muscl_gradient_kernel + K2M on any tiled layout, + K1<RECON> with --kernel gather
+        kernel_name = "gather_muscl" if kernel == GATHER else "tiled_muscl"
     op.set_options(courant=not args.no_courant)
     if world > 1:
         uid = [Operator.nccl_unique_id() if rank == 0 else None]
@@ -327,8 +330,8 @@ def run_b200_arm(args):
     if rank == 0:
         peak, peak_src = measured_peak()
         bytes_per_cell = 140 if args.hr else BYTES_PER_CELL_TRI
-        if args.second_order:  # + gradients written and read (48 + 48) + per-slot LS weights and face offsets (3 slots x 6 doubles)
-            bytes_per_cell += 96 + 144
+        if args.second_order:  # + gradients written and read (48 + 48) + per-slot LS weights (3 slots x 2 doubles) + face offsets (K1: 3 slots x 4; K2M: 1.5 edges x 4)
+            bytes_per_cell += 96 + 48 + (96 if kernel == GATHER else 48)
         achieved = bytes_per_cell * n_owned / (ms_per_step * 1e-3) / 1e9  # this rank's kernel: per-GPU figure
         traffic = recorded_traffic(kernel_name + ("_hr" if args.hr else ""))
         line = {
@@ -347,7 +350,7 @@ def run_b200_arm(args):
             },
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (traffic * n_owned if traffic else None), "peak_source": peak_src,
-                         "algorithmic_bytes_per_cell": bytes_per_cell, "kernel": "muscl_gradient_kernel + swe_gather_kernel<RECON>" if args.second_order else "swe_%s_kernel" % kernel_name,
+                         "algorithmic_bytes_per_cell": bytes_per_cell, "kernel": ("muscl_gradient_kernel + " + ("swe_gather_kernel<RECON>" if kernel == GATHER else "swe_tiled_muscl_kernel")) if args.second_order else "swe_%s_kernel" % kernel_name,
                          "note": "per-GPU: algorithmic bytes of one launch / CUDA-event time per launch on the launching stream"},
             "e2e": e2e,
             "gpu_launches": int(launches),

@@ -295,6 +295,7 @@ void rdyb_tiled_layout_free(RdybTiledLayout *T) {
   if (!T) return;
   free(T->tile_cell_begin); free(T->halo_offsets); free(T->halo_cells); free(T->edge_offsets); free(T->edge_lr);
   free(T->edge_bidx); free(T->edge_sn); free(T->edge_cn); free(T->edge_len); free(T->cell_edges); free(T->edge_id); free(T->edge_cell); free(T->tile_desc);
+  free(T->edge_off);
   memset(T, 0, sizeof(*T));
 }
 
@@ -600,4 +601,36 @@ fail:
   free(tmp_halo); free(slot_edge);
   rdyb_tiled_layout_free(T);
   return ierr;
+}
+
+/* Second-order face offsets per tile edge, derived from the per-slot MUSCL geometry (rdyb_layout_build_muscl): every tile edge is
+ * listed in cell_edges by at least one tile cell, whose slot holds midpoint - own centroid (dxs, dys) and midpoint - neighbour
+ * centroid (dxn, dyn); bit 15 of the cell_edges entry says whether that cell is the edge's right cell.  Both cells of an in-tile
+ * edge write the same doubles (the left cell's dxn IS the right cell's dxs), so the result does not depend on the visiting order
+ * nor on the optional edge schedule.  Layout: four planes of total_edges doubles {dxl, dyl, dxr, dyr}; boundary and padding
+ * edges keep 0 (boundary fluxes stay first order, ReconstructFaceValues only visits internal edges). */
+int rdyb_tiled_layout_build_muscl(const RdybLayout *L, RdybTiledLayout *T) {
+  RDYB_CHECK(L && T && T->tile_desc, RDYB_ERR_ARG, "tiled MUSCL layout: NULL argument");
+  RDYB_CHECK(L->ell_dxs && L->ell_dys && L->ell_dxn && L->ell_dyn, RDYB_ERR_USER, "tiled MUSCL layout: build the MUSCL slot geometry first");
+  free(T->edge_off);
+  const size_t plane = (size_t)T->total_edges, S = (size_t)L->stride;
+  T->edge_off = calloc(4 * (plane > 0 ? plane : 1), sizeof(double));
+  if (!T->edge_off) return rdyb_fail(RDYB_ERR_MEM, "tiled MUSCL layout: out of memory (face offsets)");
+  for (int32_t t = 0; t < T->num_tiles; ++t) {
+    const int32_t *d = &T->tile_desc[8 * (size_t)t];
+    const int32_t cb = d[0], ncell = d[1], eo = d[2], nedge = d[3];
+    for (int32_t i = cb; i < cb + ncell; ++i)
+      for (int32_t k = 0; k < L->width; ++k) {
+        const size_t q = (size_t)k * S + (size_t)i;
+        const uint16_t ce = T->cell_edges[q];
+        if (ce == 0xffffu || L->ell_nbr[q] < 0) continue;
+        const int32_t e = ce & 0x7fff;
+        if (e >= nedge) return rdyb_fail(RDYB_ERR_USER, "tiled MUSCL layout: inconsistent edge slot at cell %d", L->dev_to_local[i]);
+        const size_t g = (size_t)eo + (size_t)e;
+        const int right = (ce & 0x8000u) != 0;
+        T->edge_off[(right ? 2 : 0) * plane + g] = L->ell_dxs[q]; T->edge_off[(right ? 3 : 1) * plane + g] = L->ell_dys[q];
+        T->edge_off[(right ? 0 : 2) * plane + g] = L->ell_dxn[q]; T->edge_off[(right ? 1 : 3) * plane + g] = L->ell_dyn[q];
+      }
+  }
+  return RDYB_SUCCESS;
 }

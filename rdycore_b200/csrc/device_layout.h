@@ -84,6 +84,9 @@ typedef struct {
    * bit 15 set => the cell is the edge's right cell; 0xFFFF => empty */
   uint16_t *cell_edges;      /* [width*stride], slot-major like the ELL arrays */
   int64_t   total_edges, total_halo;
+  /* second order only (rdyb_tiled_layout_build_muscl, NULL otherwise): [4][total_edges] face offsets per tile edge,
+   * edge midpoint - centroid of the left cell (dxl, dyl) and of the right cell (dxr, dyr) */
+  double   *edge_off;
 } RdybTiledLayout;
 
 /* warp-tile layout (kernel "warp", K5): every tile of tile_cells cells is cut into mini-tiles of 32 consecutive cells, one per
@@ -119,6 +122,7 @@ int  rdyb_layout_build_muscl(const RdybMeshView *mesh, RdybLayout *layout);
 void rdyb_layout_free(RdybLayout *layout);
 int  rdyb_tiled_layout_build(const RdybLayout *layout, int32_t tile_cells, RdybTiledLayout *out);
 void rdyb_tiled_layout_free(RdybTiledLayout *tiled);
+int  rdyb_tiled_layout_build_muscl(const RdybLayout *layout, RdybTiledLayout *tiled);
 
 #ifdef __cplusplus
 }

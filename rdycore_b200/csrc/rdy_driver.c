@@ -370,6 +370,8 @@ PetscErrorCode RDySetup(RDy rdy) {
   }
   RDYB_CALL(rdyb_hostmesh_halo(rdy->mesh, &halo));
   RDYB_CALL(rdyb_operator_create(&rdy->physics, &view, rdy->num_boundaries, rdy->boundaries, halo.num_peers > 0 ? &halo : NULL, rdy->device, NULL, &rdy->op));
+  /* numerics.second_order runs the tiled MUSCL kernel, tuned for 128-cell tiles (swe_tiled_muscl.cuh), unless RDyB200SetKernel chose a shape */
+  if (rdy->physics.reconstruction && rdy->kernel_kind == 3 && rdy->tile_cells == 224) rdy->tile_cells = 128;
   RDYB_CALL(rdyb_operator_set_kernel(rdy->op, rdy->kernel_kind, rdy->tile_cells));
   RDYB_CALL(rdyb_operator_set_options(rdy->op, 1, 0, 0, 0));
   rdy->time = 0.0; rdy->step = 0;

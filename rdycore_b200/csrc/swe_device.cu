@@ -23,6 +23,7 @@
 #include "swe_tiled_async.cuh"
 #include "swe_tiled_fixed.cuh"
 #include "swe_tiled_split.cuh"
+#include "swe_tiled_muscl.cuh"
 #include "swe_warp.cuh"
 
 static std::atomic<int64_t> g_launches{0};
@@ -107,6 +108,8 @@ struct RdybOperator_ {
   /* second order (MUSCL): reconstruction kind (RDYB_RECON_*, 0 = first order), cell gradients [6][stride], per-slot geometry */
   int recon = 0;
   double *grad = nullptr, *m_gcx = nullptr, *m_gcy = nullptr, *m_dxs = nullptr, *m_dys = nullptr, *m_dxn = nullptr, *m_dyn = nullptr;
+  double *t_edge_off = nullptr; /* [4][T.total_edges] face offsets per tile edge: the second-order path on the tiled layout (K2M) */
+  bool courant_arg_tiled = false; /* the Courant arg of the last launch is a tile-edge index (else device cell * ELL width + slot) */
   bool ghosts_from_caller = false; /* host-Vec apply: u_local arrives with its ghosts filled (DMGlobalToLocal already ran) */
   /* tiled-kernel device arrays */
   TiledDev td;
@@ -196,7 +199,7 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
                   op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
                   op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y, op->grad, op->m_gcx, op->m_gcy, op->m_dxs, op->m_dys,
-                  op->m_dxn, op->m_dyn};
+                  op->m_dxn, op->m_dyn, op->t_edge_off};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (void *p : {(void *)op->pipe.order, (void *)op->pipe.local_to_dev, (void *)op->pipe.owned_to_dev, (void *)op->pipe.stage_in, (void *)op->pipe.stage_out})
@@ -281,7 +284,8 @@ static int operator_create_impl(RdybOperator op, const RdybConfig *config, const
   }
   op->ncblocks_interior = grid_for(op->NI, RDYB_BLOCK);
   op->ncblocks = op->ncblocks_interior + grid_for(op->N - op->NI, RDYB_BLOCK) + 1;
-  /* the tiled kernel needs one slot per tile; tiles are never smaller than RDYB_BLOCK cells, so ncblocks covers both */
+  /* the tiled kernels need one slot per tile (K2, K2M) or per resident block: set_kernel grows the arrays when a tiled layout has
+   * more tiles than this (short frontier tiles) */
   RDYB_CALL(dalloc(&op->cmax, (size_t)op->ncblocks)); RDYB_CALL(dalloc(&op->carg, (size_t)op->ncblocks));
   CU(cudaMemset(op->carg, 0xff, sizeof(long long) * (size_t)op->ncblocks));
   RDYB_CALL(dalloc(&op->partial, 1024));
@@ -338,6 +342,18 @@ extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_
 }
 
 static void pipe_release(RdybOperator op);
+/* one Courant slot per tile for the kernels that index them by tile number */
+static int ensure_courant_slots(RdybOperator op, int32_t n) {
+  if (n <= op->ncblocks) return RDYB_SUCCESS;
+  CU(cudaStreamSynchronize(op->stream));
+  if (op->cmax) cudaFree(op->cmax);
+  if (op->carg) cudaFree(op->carg);
+  op->cmax = nullptr; op->carg = nullptr;
+  op->ncblocks = n;
+  RDYB_CALL(dalloc(&op->cmax, (size_t)n)); RDYB_CALL(dalloc(&op->carg, (size_t)n));
+  CU(cudaMemset(op->carg, 0xff, sizeof(long long) * (size_t)n));
+  return RDYB_SUCCESS;
+}
 /* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
@@ -347,6 +363,7 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
     if (op->has_tiled && op->T.tile_cells != tile_cells) {
       tiled_dev_free(&op->td);
       rdyb_tiled_layout_free(&op->T);
+      if (op->t_edge_off) { cudaFree(op->t_edge_off); op->t_edge_off = nullptr; }
       op->has_tiled = false;
       pipe_release(op);
       fpush_release(op);
@@ -354,6 +371,11 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
     if (!op->has_tiled) {
       RDYB_CALL(rdyb_tiled_layout_build(&op->L, tile_cells, &op->T));
       RDYB_CALL(tiled_dev_upload(&op->T, &op->L, &op->td));
+      RDYB_CALL(ensure_courant_slots(op, op->T.num_tiles + 1));
+      if (op->recon && !getenv("RDYB_MUSCL_K1")) { /* second order on the tiled layout (K2M); RDYB_MUSCL_K1 keeps it on K1 */
+        RDYB_CALL(rdyb_tiled_layout_build_muscl(&op->L, &op->T));
+        RDYB_CALL(upload(&op->t_edge_off, op->T.edge_off, 4 * (size_t)op->T.total_edges));
+      }
       op->has_tiled = true;
     }
   }
@@ -579,7 +601,22 @@ static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
 /* one RHS / Euler pass over owned device cells [begin,end) */
 static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
   if (end <= begin) return RDYB_SUCCESS;
-  if (op->kernel_kind >= 1 && op->has_tiled && !op->recon) { /* the second-order path runs on K1 */
+  op->courant_arg_tiled = false;
+  if (op->recon && op->kernel_kind >= 1 && op->has_tiled && begin == 0 && end == op->N && tiled_muscl_applicable(op->T, op->t_edge_off)) {
+    /* second order on the tiled layout: every tiled kind runs K2M (one launch over all tiles; the state and gradient halos are complete) */
+    SweArgs t;
+    fill_args(op, t, in, out, dt);
+    t.begin = begin; t.end = end;
+    if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile */
+    op->last_kernel = "swe_tiled_muscl_kernel (K2M, MUSCL) + muscl_gradient_kernel";
+    op->courant_arg_tiled = true;
+    RDYB_CALL(tiled_muscl_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));
+    LAUNCHED();
+    CU(cudaGetLastError());
+    return RDYB_SUCCESS;
+  }
+  if (op->kernel_kind >= 1 && op->has_tiled && !op->recon) { /* first order: the tiled kernels */
+    op->courant_arg_tiled = true;
     /* interior tiles and frontier tiles (thin strips along the partition border, with many more outside neighbours) are
      * launched separately so that each part can use the most specialised kernel its tiles fit */
     SweArgs t;
@@ -1127,7 +1164,7 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
     /* warp kernel: arg = global mini-tile-edge index */
     d->global_edge_id = op->WL.edge_id[arg];
     d->global_cell_id = op->L.dev_to_local[op->WL.edge_cell[arg]];
-  } else if (arg >= 0 && op->kernel_kind >= 1 && op->has_tiled) {
+  } else if (arg >= 0 && op->courant_arg_tiled && op->has_tiled) {
     /* tiled kernel: arg = global tile-edge index */
     d->global_edge_id = op->T.edge_id[arg];
     d->global_cell_id = op->L.dev_to_local[op->T.edge_cell[arg]];

@@ -136,6 +136,8 @@ class HostMesh:
         }
         if v.cell_zc:
             out["cell_zc"] = _as(v.cell_zc, nc, np.float64)
+        if v.edge_xm and v.edge_ym:
+            out["edge_xm"], out["edge_ym"] = _as(v.edge_xm, ne, np.float64), _as(v.edge_ym, ne, np.float64)
         return out
 
     def halo_arrays(self) -> dict:

@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from rdycore_b200 import cases
-from rdycore_b200.operator import GATHER, TILED_FIXED, Operator
+from rdycore_b200.operator import GATHER, TILED, TILED_FIXED, Operator
 
 from util import assert_state_close, make_oracle
 
@@ -30,14 +30,14 @@ def test_dam_break_quads_second_order(reconstruction, source_method):
     case.config.reconstruction = reconstruction
     oracle = make_oracle(case)
     op = Operator.from_case(case)
-    op.set_kernel(TILED_FIXED, 224)  # a tiled kernel may be selected: the second-order path still runs (on K1)
+    op.set_kernel(TILED_FIXED, 224)  # any tiled kind runs the second-order path on the tiled layout (K2M, swe_tiled_muscl.cuh)
     # Van Leer's smooth limiter amplifies round-off faster than minmod: the CPU port compiled with and without FMA contraction
     # (scratch/fma/sens.py, same C source) differs by 4e-12 / 9e-12 / 1.7e-11 after 100 / 200 / 400 steps on this case, the
     # GPU by 1.15e-11 after 400 — so the 1e-11 tolerance is checked at 150 steps there, 400 for minmod and unlimited.
     steps = 150 if reconstruction == cases.MUSCL_VANLEER else 400
     op.step_euler(case.dt, steps)
     oracle.step_euler(case.dt, steps)
-    assert "MUSCL" in op.kernel_info()
+    assert "K2M, MUSCL" in op.kernel_info()
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order dam break")
     first = cases.dam_break_quads(nx=60, ny=60, source_method=source_method)
     o1 = make_oracle(first)
@@ -45,11 +45,13 @@ def test_dam_break_quads_second_order(reconstruction, source_method):
     assert np.abs(o1.array("u_global") - oracle.array("u_global")).max() > 1e-2  # it really is a different scheme
 
 
+@pytest.mark.parametrize("kernel", [GATHER, TILED])
 @pytest.mark.parametrize("reconstruction", [cases.MUSCL_MINMOD, cases.MUSCL_VANLEER])
-def test_wet_triangle_floodplain_second_order(reconstruction):
+def test_wet_triangle_floodplain_second_order(reconstruction, kernel):
     case = _wet_floodplain(reconstruction)
     oracle = make_oracle(case)
     op = Operator.from_case(case)
+    op.set_kernel(kernel, 128)
     if reconstruction == cases.MUSCL_VANLEER:
         # van Leer + forward Euler is unstable on this rough state (the oracle itself reaches NaN by step 200): RK4 there
         op.step_rk4(case.dt, 100)
@@ -60,10 +62,12 @@ def test_wet_triangle_floodplain_second_order(reconstruction):
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order floodplain")
 
 
-def test_second_order_rhs_courant_and_rk4():
+@pytest.mark.parametrize("kernel", [GATHER, TILED])
+def test_second_order_rhs_courant_and_rk4(kernel):
     case = _wet_floodplain(cases.MUSCL_MINMOD)
     oracle = make_oracle(case)
     op = Operator.from_case(case)
+    op.set_kernel(kernel, 224)
     op.set_options(courant=True, flux_divergence=True)
     F_ref = oracle.rhs(case.dt).reshape(-1, 3).copy()
     F = op.apply_host(case.dt, oracle.array("u_local"))
@@ -72,6 +76,10 @@ def test_second_order_rhs_courant_and_rk4():
     fd = oracle.array("flux_divergence").reshape(-1, 3)
     assert (np.abs(op.get_field(0) - fd) / np.abs(fd).max(axis=0)).max() < 1e-12
     assert op.courant().max_courant_num == pytest.approx(oracle.courant(), rel=1e-12)
+    assert ("K2M" in op.kernel_info()) == (kernel == TILED)
+    d = op.courant()  # the arg of the maximum names an internal edge and one of its two cells, whichever kernel reported it
+    ecells = case.mesh.view_arrays()["edge_cell_ids"].reshape(-1, 2)
+    assert d.global_cell_id in ecells[d.global_edge_id] and ecells[d.global_edge_id].min() >= 0
     op.set_state(case.u0)
     op.step_rk4(case.dt, 40)
     oracle.array("u_global")[:] = case.u0.ravel()
@@ -79,8 +87,35 @@ def test_second_order_rhs_courant_and_rk4():
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order RK4")
     # bitwise repeatable
     op2 = Operator.from_case(case)
+    op2.set_kernel(kernel, 224)
     op2.step_rk4(case.dt, 40)
     assert np.array_equal(op2.get_state(), op.get_state())
+
+
+@pytest.mark.parametrize("reconstruction", LIMITERS)
+def test_tiled_and_gather_second_order_agree(reconstruction, monkeypatch):
+    """K2M solves every edge once from shared memory, K1 twice from global memory: same face states, same fluxes; only the
+    association of flux * length / area differs, so one right-hand side agrees to round-off.  RDYB_MUSCL_K1 keeps K1 on a tiled layout."""
+    case = _wet_floodplain(reconstruction)
+    ops = []
+    for kind, env in ((TILED, None), (GATHER, None), (TILED_FIXED, "1")):
+        if env:
+            monkeypatch.setenv("RDYB_MUSCL_K1", env)
+        op = Operator.from_case(case)
+        op.set_kernel(kind, 160)
+        op.set_options(courant=True)
+        ops.append(op)
+    oracle = make_oracle(case)
+    oracle.rhs(case.dt)  # fills u_local from the initial state
+    u_local = oracle.array("u_local")
+    assert np.abs(u_local.reshape(-1, 3)[:, 1:]).max() > 0.0
+    F = [op.apply_host(case.dt, u_local) for op in ops]
+    assert "K2M" in ops[0].kernel_info() and "K1, MUSCL" in ops[1].kernel_info() and "K1, MUSCL" in ops[2].kernel_info()
+    scale = np.abs(F[1]).max(axis=0)
+    assert (np.abs(F[0] - F[1]) / scale).max() < 1e-14
+    assert np.array_equal(F[1], F[2])
+    c = [op.courant().max_courant_num for op in ops]
+    assert c[0] == pytest.approx(c[1], rel=1e-14) and c[1] == c[2]
 
 
 def test_hr_with_second_order_is_refused_like_the_reference():
