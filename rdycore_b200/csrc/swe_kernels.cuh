@@ -42,7 +42,7 @@ struct SweArgs {
   long long *__restrict__ carg;
   int32_t stride, width, begin, end;
   double dt, tiny_h, ha2, xq_thr;
-  /* second order (MUSCL, K1 only): cell gradients SoA [6][stride] = d/dx (h,hu,hv), d/dy (h,hu,hv) incl. ghost cells, and the
+  /* second order (MUSCL; K2M reads grad only, the per-slot arrays are for K1 and the gradient kernel): cell gradients SoA [6][stride] = d/dx (h,hu,hv), d/dy (h,hu,hv) incl. ghost cells, and the
    * per-slot least-squares weights / face offsets of device_layout.h; all NULL for first order */
   const double *__restrict__ grad;
   const double *__restrict__ gcx, *__restrict__ gcy, *__restrict__ dxs, *__restrict__ dys, *__restrict__ dxn, *__restrict__ dyn;
