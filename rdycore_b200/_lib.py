@@ -127,4 +127,4 @@ def lib() -> C.CDLL:
 
 def check(code: int) -> None:
     if code != 0:
-        raise RdybError(code, lib().rdyb_last_error().decode())
+        raise RdybError(code, lib().rdyb_last_error().decode(errors="replace"))

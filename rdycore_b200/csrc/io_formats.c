@@ -52,7 +52,7 @@ int rdyb_petsc_vec_read(const char *path, int64_t *n, double **values, int32_t *
   int64_t count = -1;
   if (len >= 8 && be32(b) == RDYB_VEC_FILE_CLASSID) { hdr = 8; count = (int64_t)be32(b + 4); }
   else if (len >= 16 && be64(b) == RDYB_VEC_FILE_CLASSID) { hdr = 16; count = (int64_t)be64(b + 8); }
-  if (count < 0 || hdr + 8 * (size_t)count > len) {
+  if (count < 0 || (uint64_t)count > (len - hdr) / 8) { /* hdr <= len whenever count >= 0 */
     free(b);
     return rdyb_fail(RDYB_ERR_USER, "%s is not a PETSc binary Vec (no VEC_FILE_CLASSID header, or truncated)", path);
   }
@@ -181,7 +181,7 @@ static int nc_open(NcFile *f, const unsigned char *b, size_t len, const char *pa
       v->nelems = 1;
       for (uint32_t d = 0; d < nd; ++d) {
         const uint32_t id = nc_u32(f);
-        if ((int)id >= f->ndims) { f->bad = 1; break; }
+        if (id >= (uint32_t)f->ndims) { f->bad = 1; break; }
         v->dimids[d] = (int)id;
         if (d == 0 && f->dims[id].len == 0) v->is_record = 1;
         else v->nelems *= f->dims[id].len;
@@ -212,7 +212,8 @@ static int nc_read_double(const NcFile *f, const NcVar *v, double *out, int64_t 
   RDYB_CHECK(v && !v->is_record && v->nelems == expect && (v->type == NC_DOUBLE || v->type == NC_FLOAT), RDYB_ERR_USER, "%s: variable %s has an unexpected shape or type",
              path, v ? v->name : "(missing)");
   const size_t sz = nc_type_size(v->type);
-  RDYB_CHECK(v->begin + sz * (uint64_t)expect <= f->len, RDYB_ERR_USER, "%s: variable %s runs past the end of the file", path, v->name);
+  RDYB_CHECK(expect >= 0 && v->begin <= f->len && (uint64_t)expect <= (f->len - v->begin) / sz, RDYB_ERR_USER, "%s: variable %s runs past the end of the file", path,
+             v->name);
   for (int64_t i = 0; i < expect; ++i) {
     const unsigned char *p = f->b + v->begin + sz * (size_t)i;
     if (v->type == NC_DOUBLE) out[i] = bef64(p);
@@ -223,7 +224,8 @@ static int nc_read_double(const NcFile *f, const NcVar *v, double *out, int64_t 
 static int nc_read_int(const NcFile *f, const NcVar *v, int32_t *out, int64_t expect, const char *path) {
   RDYB_CHECK(v && !v->is_record && v->nelems == expect && v->type == NC_INT, RDYB_ERR_USER, "%s: variable %s has an unexpected shape or type", path,
              v ? v->name : "(missing)");
-  RDYB_CHECK(v->begin + 4 * (uint64_t)expect <= f->len, RDYB_ERR_USER, "%s: variable %s runs past the end of the file", path, v->name);
+  RDYB_CHECK(expect >= 0 && v->begin <= f->len && (uint64_t)expect <= (f->len - v->begin) / 4, RDYB_ERR_USER, "%s: variable %s runs past the end of the file", path,
+             v->name);
   for (int64_t i = 0; i < expect; ++i) out[i] = (int32_t)be32(f->b + v->begin + 4 * (size_t)i);
   return RDYB_SUCCESS;
 }
@@ -251,6 +253,11 @@ static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
   int64_t nd = nc_dim(f, "num_dim"), nss = nc_dim(f, "num_side_sets");
   RDYB_CHECK(nn > 0 && ne > 0 && nb > 0 && nd >= 2 && nd <= 3, RDYB_ERR_USER, "%s is not an Exodus II mesh (num_nodes/num_elem/num_el_blk/num_dim missing)", path);
   if (nss < 0) nss = 0;
+  /* sizes a file of this length can hold (>= 4 bytes per coordinate and per connectivity entry; one dimension per block and per
+   * side set): a corrupt header must not drive the allocations and loops below */
+  RDYB_CHECK((uint64_t)nn <= f->len / 4 && (uint64_t)ne <= f->len / 12 && nb <= f->ndims && nss <= f->ndims, RDYB_ERR_USER,
+             "%s: corrupt Exodus II header (%lld nodes, %lld elements, %lld blocks, %lld side sets in a file of %zu bytes)", path, (long long)nn, (long long)ne,
+             (long long)nb, (long long)nss, f->len);
   m->num_dim = (int32_t)nd; m->num_nodes = (int32_t)nn; m->num_elems = (int32_t)ne; m->num_blocks = (int32_t)nb; m->num_side_sets = (int32_t)nss;
   m->x = (double *)calloc((size_t)nn, 8); m->y = (double *)calloc((size_t)nn, 8); m->z = (double *)calloc((size_t)nn, 8);
   m->elem_offsets = (int32_t *)calloc((size_t)ne + 1, 4); m->elem_block = (int32_t *)calloc((size_t)ne, 4); m->block_ids = (int32_t *)calloc((size_t)nb, 4);
@@ -282,8 +289,10 @@ static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
     const int64_t npe = nc_dim(f, name);
     RDYB_CHECK(nel >= 0 && npe >= 3 && npe <= 4, RDYB_ERR_USER, "%s: element block %lld has %lld nodes per element (only triangles and quadrilaterals are supported)",
                path, (long long)b + 1, (long long)npe);
+    RDYB_CHECK(nel <= ne, RDYB_ERR_USER, "%s: element block %lld holds %lld elements, num_elem says %lld", path, (long long)b + 1, (long long)nel, (long long)ne);
     total += nel * npe;
   }
+  RDYB_CHECK(total <= 4 * ne, RDYB_ERR_USER, "%s: element blocks hold more elements than num_elem (%lld)", path, (long long)ne);
   m->elem_nodes = (int32_t *)calloc((size_t)(total > 0 ? total : 1), 4);
   char *et8 = (char *)calloc((size_t)ne, 8); /* first 7 characters of the element type, per element */
   RDYB_CHECK(m->elem_nodes && et8, RDYB_ERR_MEM, "out of memory");
@@ -297,6 +306,7 @@ static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
     snprintf(name, sizeof(name), "connect%lld", (long long)b + 1);
     const NcVar *cv = nc_var(f, name);
     if (nel == 0) continue;
+    if (e0 + nel > ne) { rc = rdyb_fail(RDYB_ERR_USER, "%s: element blocks hold more than the %lld elements num_elem says", path, (long long)ne); break; }
     rc = nc_read_int(f, cv, m->elem_nodes + pos, nel * npe, path);
     if (rc) break;
     for (int64_t k = 0; k < nel * npe; ++k) {
@@ -323,11 +333,13 @@ static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
       const int64_t k = nc_dim(f, name);
       m->side_set_offsets[s] = (int32_t)nsides;
       nsides += k > 0 ? k : 0;
+      if ((uint64_t)nsides > f->len / 8) rc = rdyb_fail(RDYB_ERR_USER, "%s: corrupt side set sizes (%lld sides in a file of %zu bytes)", path, (long long)nsides, f->len);
     }
+    if (rc) nsides = 0;
     m->side_set_offsets[nss] = (int32_t)nsides;
     m->side_elems = (int32_t *)calloc((size_t)(nsides > 0 ? nsides : 1), 4);
     m->side_edges = (int32_t *)calloc((size_t)(nsides > 0 ? nsides : 1), 4);
-    if (!m->side_elems || !m->side_edges) rc = rdyb_fail(RDYB_ERR_MEM, "out of memory");
+    if (!rc && (!m->side_elems || !m->side_edges)) rc = rdyb_fail(RDYB_ERR_MEM, "out of memory");
     for (int64_t s = 0; s < nss && !rc; ++s) {
       const int64_t k = m->side_set_offsets[s + 1] - m->side_set_offsets[s], o = m->side_set_offsets[s];
       if (k == 0) continue;
@@ -506,7 +518,7 @@ int rdyb_checkpoint_read(const char *path, RdybCheckpointMetadata *md, int64_t *
     if (!ierr) {
       const int64_t count = GET_INT(k) == RDYB_VEC_FILE_CLASSID ? GET_INT(k + (size_t)ib) : -1;
       k += 2 * (size_t)ib;
-      if (count < 0 || k + 8 * (size_t)count > len) ierr = rdyb_fail(RDYB_ERR_USER, "%s: no solution Vec after the metadata, or truncated", path);
+      if (count < 0 || k > len || (uint64_t)count > (len - k) / 8) ierr = rdyb_fail(RDYB_ERR_USER, "%s: no solution Vec after the metadata, or truncated", path);
       else {
         double *v = (double *)malloc(8 * (size_t)(count > 0 ? count : 1));
         if (!v) ierr = rdyb_fail(RDYB_ERR_MEM, "out of memory reading %s", path);

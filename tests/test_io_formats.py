@@ -138,3 +138,27 @@ def test_checkpoint_errors(tmp_path):
         io.read_checkpoint(p)
     with pytest.raises(RuntimeError, match="out of range"):
         io.write_checkpoint(str(tmp_path / "w.bin"), np.zeros((2, 3)), 0.0, 1.0, 0, num_global_cells=2, natural_ids=np.array([0, 5]))
+
+
+# ---- corrupt input: the readers answer with an error, never a crash (mutation fuzz, scratch/fuzz/fuzz_readers.py runs it at length) ----
+@pytest.mark.parametrize("fixture,kind,seed", [
+    ("mms_triangles_dx1.exo", "exo", 0),   # crashed before the header sanity checks: element blocks larger than num_elem
+    ("quad_tri_mesh.exo", "exo", 2),       # crashed: dimension id >= 2^31 in a variable's dimension list
+    ("levee.exo", "exo", 5),
+    ("DamBreak_grid5x10_wetdownstream.ic.int64.bin", "vec", 1),
+    ("checkpoint", "ck", 3),
+])
+def test_mutated_files_never_crash_the_readers(tmp_path, fixture, kind, seed):
+    import subprocess
+    import sys
+
+    src = os.path.join(FIX, fixture)
+    if kind == "ck":
+        src = str(tmp_path / "src.rdycore.r.bin")
+        io.write_checkpoint(src, np.arange(90.0).reshape(30, 3), t=1.0, dt=0.1, step=10, nproc=2, index_bytes=8)
+    tmp = str(tmp_path / ("mutant.bin" if kind != "exo" else "mutant.exo"))
+    r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "reader_fuzz.py"), src, kind, str(seed), "50", tmp],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, f"reader crashed (rc {r.returncode}) after trial {r.stdout.strip().splitlines()[-1:]}: {r.stderr[-300:]}"
+    ok, err = map(int, r.stdout.strip().splitlines()[-1].split()[1:])
+    assert ok + err == 50 and err > 0
