@@ -47,6 +47,15 @@ def _layouts(case, tile_cells, halo=None):
     return view, L, T
 
 
+def _layouts_first_order(case, tile_cells, halo=None):
+    view = case.mesh.view()
+    arr, nb = case.boundary_views()
+    L, T = RdybLayout(), RdybTiledLayout()
+    check(lib().rdyb_layout_build(C.byref(view), C.c_int32(nb), arr, C.byref(halo) if halo is not None else None, C.c_int(1), C.byref(L)))
+    check(lib().rdyb_tiled_layout_build(C.byref(L), C.c_int32(tile_cells), C.byref(T)))
+    return view, L, T
+
+
 def _check_offsets(case, tile_cells, halo=None):
     view, L, T = _layouts(case, tile_cells, halo)
     try:
@@ -88,8 +97,10 @@ def test_tile_edge_face_offsets_triangles(tile_cells):
     assert n_int >= (3 * n_cells - n_bnd) // 2  # every internal edge once, edges between two tiles twice
 
 
-def test_tile_edge_face_offsets_with_ghosts():
-    """A 2-rank block partition: frontier tiles are short and list ghost cells in their halo; offsets of owned-ghost edges included."""
+def test_tile_edge_face_offsets_with_ghosts(monkeypatch):
+    """A 2-rank block partition: frontier tiles are short and list ghost cells in their halo; offsets of owned-ghost edges included.
+    Built with the opt-in edge schedule, which permutes the tile edges after they were created."""
+    monkeypatch.setenv("RDYB_EDGE_SCHEDULE", "1")
     case = cases.floodplain(nx=40, ny=24, eta0=40.0, px=2, py=1, rank=1)
     case.config.reconstruction = cases.MUSCL_VANLEER
     halo = case.mesh.halo()
@@ -108,3 +119,70 @@ def test_tiled_muscl_layout_needs_the_slot_geometry():
     assert b"slot geometry" in lib().rdyb_last_error()
     lib().rdyb_tiled_layout_free(C.byref(T))
     lib().rdyb_layout_free(C.byref(L))
+
+
+NO_EDGE = -2**31
+
+
+@pytest.mark.parametrize("schedule", [False, True])
+@pytest.mark.parametrize("partitioned", [False, True])
+@pytest.mark.parametrize("tile_cells", [128, 224])
+def test_tiled_layout_invariants(tile_cells, partitioned, schedule, monkeypatch):
+    """What the tiled kernels (K2-K6, K2M) assume about a tile: padded slices, a sorted halo outside the tile, edges with at least one
+    tile cell, per-cell edge slots that mirror the ELL slots (same edge, same side, same geometry, same order), short frontier tiles."""
+    if schedule:  # the opt-in bank-aware edge order permutes a tile's edges; every invariant must survive it
+        monkeypatch.setenv("RDYB_EDGE_SCHEDULE", "1")
+    if partitioned:
+        case = cases.floodplain(nx=44, ny=30, eta0=8.0, px=2, py=1, rank=0)
+        halo = case.mesh.halo()
+    else:
+        case, halo = cases.dam_break_quads(nx=30, ny=22), None
+    view, L, T = _layouts_first_order(case, tile_cells, halo)
+    try:
+        S, W, TC, N, NI = L.stride, L.width, T.tile_cells, L.n_owned, L.n_interior
+        plane = T.total_edges
+        desc = _np(T.tile_desc, 8 * T.num_tiles).reshape(-1, 8)
+        lr, eid, bidx = _np(T.edge_lr, plane), _np(T.edge_id, plane), _np(T.edge_bidx, plane)
+        esn, ecn, elen = _np(T.edge_sn, plane), _np(T.edge_cn, plane), _np(T.edge_len, plane)
+        halo_cells = _np(T.halo_cells, T.total_halo)
+        cell_edges = _np(T.cell_edges, 4 * S).reshape(4, S)
+        nbr, slen = _np(L.ell_nbr, 4 * S).reshape(4, S), _np(L.ell_slen, 4 * S).reshape(4, S)
+        lsn, lcn, ledge = _np(L.ell_sn, 4 * S).reshape(4, S), _np(L.ell_cn, 4 * S).reshape(4, S), _np(L.ell_edge, 4 * S).reshape(4, S)
+        assert NI < N if partitioned else NI == N
+        covered = 0
+        for t, (cb, ncell, eo, nedge, ho, nhalo, _, _) in enumerate(desc):
+            interior = t < T.num_interior_tiles
+            assert eo % 4 == 0 and ho % 4 == 0 and 0 < ncell <= TC and cb == covered
+            covered += ncell
+            assert (cb + ncell <= NI) if interior else (cb >= NI)
+            h = halo_cells[ho:ho + nhalo]
+            assert np.all(np.diff(h) > 0) and not np.any((h >= cb) & (h < cb + ncell)) and np.all((h >= 0) & (h < L.n_local))
+            if interior:
+                assert np.all(h < N)  # interior cells have no ghost neighbour
+            else:
+                assert ncell <= 80 // W and nhalo <= 80 and nedge <= 80  # frontier tiles fit every compiled tile shape
+            used = np.zeros(nedge, bool)
+            for i in range(cb, cb + ncell):
+                for k in range(W):
+                    ce = int(cell_edges[k, i])
+                    if nbr[k, i] == NO_EDGE:
+                        assert ce == 0xFFFF
+                        continue
+                    e, right = ce & 0x7FFF, bool(ce & 0x8000)
+                    assert e < nedge and right == (slen[k, i] > 0)
+                    g = eo + e
+                    used[e] = True
+                    l, r = int(lr[g]) & 0xFFFF, int(lr[g]) >> 16
+                    assert (r if right else l) == i - cb
+                    other = l if right else r
+                    if nbr[k, i] < 0:  # boundary slot
+                        assert other == 0xFFFF and not right and bidx[g] == -(nbr[k, i] + 1)
+                    else:
+                        dev = cb + other if other < ncell else h[other - TC]
+                        assert dev == nbr[k, i] and bidx[g] == -1
+                    assert eid[g] == ledge[k, i] and esn[g] == lsn[k, i] and ecn[g] == lcn[k, i] and elen[g] == abs(slen[k, i])
+            assert used.all()  # no tile edge without a tile cell
+        assert covered == N
+    finally:
+        lib().rdyb_tiled_layout_free(C.byref(T))
+        lib().rdyb_layout_free(C.byref(L))
