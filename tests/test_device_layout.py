@@ -186,3 +186,83 @@ def test_tiled_layout_invariants(tile_cells, partitioned, schedule, monkeypatch)
     finally:
         lib().rdyb_tiled_layout_free(C.byref(T))
         lib().rdyb_layout_free(C.byref(L))
+
+
+@pytest.mark.parametrize("which", ["quads", "triangles_rank0", "triangles_rank1", "mixed"])
+def test_cell_centric_layout_mirrors_the_mesh(which):
+    """The ELL layout every kernel is derived from (rdyb_layout_build): renumbering (interior, frontier, ghosts grouped by peer), and per
+    slot the mesh edge with its orientation, normal, length — in the order in which the reference accumulates into a cell: interior
+    edges by position in internal_edge_ids (src/swe/swe_petsc.c:244-310), then boundary edges by boundary (operator_fluxes_petsc.c:28-51)."""
+    halo = None
+    if which == "quads":
+        case = cases.dam_break_quads(nx=26, ny=18)
+    elif which == "mixed":
+        ex = __import__("rdycore_b200.io", fromlist=["io"])
+        import os
+        e = ex.read_exodus(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_fixtures", "DamBreak_grid5x10_mixed_elements.exo"))
+        mesh = ex.mesh_from_exodus(e)
+        bnd = ex.boundaries_from_side_sets(mesh, e)
+        n = mesh.num_owned_cells
+        case = cases.Case("mixed", mesh, cases.make_config(), bnd, np.ones((n, 3)), np.full(n, 0.02), None, 1e-3)
+    else:
+        case = cases.floodplain(nx=30, ny=22, eta0=8.0, px=2, py=1, rank=int(which[-1]))
+        halo = case.mesh.halo()
+    view = case.mesh.view()
+    arr, nb = case.boundary_views()
+    L = RdybLayout()
+    check(lib().rdyb_layout_build(C.byref(view), C.c_int32(nb), arr, C.byref(halo) if halo is not None else None, C.c_int(1), C.byref(L)))
+    try:
+        va = case.mesh.view_arrays()
+        N, NI, NL, S, W = L.n_owned, L.n_interior, L.n_local, L.stride, L.width
+        assert N == view.num_owned_cells and S % 32 == 0 and S >= NL and W == (3 if which.startswith("tri") else 4)
+        d2l, l2d = _np(L.dev_to_local, NL), _np(L.local_to_dev, L.num_view_cells)
+        assert len(set(d2l.tolist())) == NL and all(l2d[d2l[d]] == d for d in range(NL))
+        owned = va["cell_is_owned"]
+        assert owned[d2l[:N]].all() and not owned[d2l[N:]].any()
+        o2d, d2o = _np(L.owned_to_dev, N), _np(L.dev_to_owned, N)
+        assert np.array_equal(o2d[d2o], np.arange(N)) and np.array_equal(va["cell_local_to_owned"][d2l[:N]], d2o)
+        nbr, slen = _np(L.ell_nbr, 4 * S).reshape(4, S), _np(L.ell_slen, 4 * S).reshape(4, S)
+        sn, cn, eedge = _np(L.ell_sn, 4 * S).reshape(4, S), _np(L.ell_cn, 4 * S).reshape(4, S), _np(L.ell_edge, 4 * S).reshape(4, S)
+        ecells, elen, esn, ecn = va["edge_cell_ids"].reshape(-1, 2), va["edge_lengths"], va["edge_sn"], va["edge_cn"]
+        pos_in_internal = {int(e): p for p, e in enumerate(va["internal_edge_ids"])}
+        assert np.array_equal(_np(L.inv_area, NL), 1.0 / va["cell_areas"][d2l]) and np.array_equal(_np(L.area, NL), va["cell_areas"][d2l])
+        b_off, b_cell = _np(L.b_offsets, L.num_boundaries + 1), _np(L.b_cell, max(L.num_boundary_edges, 1))
+        flat_edges = np.concatenate([np.asarray(b.edge_ids, dtype=np.int64) for b in case.boundaries]) if case.boundaries else np.zeros(0, np.int64)
+        assert L.num_boundaries == nb and b_off[-1] == len(flat_edges) == L.num_boundary_edges
+        seen_edges = extras = 0
+        for i in range(N):
+            me, last_int, last_bnd, ghost_nbrs = d2l[i], -1, -1, 0
+            for k in range(4):
+                if nbr[k, i] == NO_EDGE:
+                    continue
+                assert k < W
+                e = eedge[k, i]
+                seen_edges += 1
+                assert abs(slen[k, i]) == elen[e] and sn[k, i] == esn[e] and cn[k, i] == ecn[e]
+                if nbr[k, i] >= 0:
+                    left = slen[k, i] < 0
+                    assert list(ecells[e]) == ([me, d2l[nbr[k, i]]] if left else [d2l[nbr[k, i]], me])
+                    assert last_bnd < 0 and pos_in_internal[int(e)] > last_int  # reference accumulation order
+                    last_int = pos_in_internal[int(e)]
+                    ghost_nbrs += nbr[k, i] >= N
+                else:
+                    j = -(nbr[k, i] + 1)
+                    assert slen[k, i] < 0 and ecells[e][0] == me and ecells[e][1] < 0 and flat_edges[j] == e and b_cell[j] == i and j > last_bnd
+                    last_bnd = j
+            if i < NI:
+                assert ghost_nbrs == 0  # interior cells run before the halo arrives: none may read a ghost
+            else:
+                extras += ghost_nbrs == 0
+        # the interior range ends on a multiple of 16 cells (aligned slices for bulk copies): at most 15 interior cells ride with the frontier
+        assert extras == 0 if NI == N else (NI % 16 == 0 and extras < 16)
+        n_int_owned_sides = sum(int(owned[c]) for e in va["internal_edge_ids"] for c in ecells[e])
+        n_bnd = sum(1 for j in range(len(flat_edges)) if b_cell[j] >= 0)
+        assert seen_edges == n_int_owned_sides + n_bnd
+        if halo is not None:  # ghosts sit after the owned cells, grouped by the rank that owns them, in the halo plan's receive order
+            h = case.mesh.halo_arrays()
+            ro = _np(L.recv_offsets, L.num_peers + 1)
+            assert L.num_peers == len(h["peer_ranks"]) and np.array_equal(ro, h["recv_offsets"]) and N + ro[-1] == NL
+            assert np.array_equal(d2l[N:], h["recv_cells"])
+            assert np.array_equal(d2l[_np(L.send_cells, h["send_offsets"][-1])], h["send_cells"])
+    finally:
+        lib().rdyb_layout_free(C.byref(L))
