@@ -607,13 +607,14 @@ fail:
  * listed in cell_edges by at least one tile cell, whose slot holds midpoint - own centroid (dxs, dys) and midpoint - neighbour
  * centroid (dxn, dyn); bit 15 of the cell_edges entry says whether that cell is the edge's right cell.  Both cells of an in-tile
  * edge write the same doubles (the left cell's dxn IS the right cell's dxs), so the result does not depend on the visiting order
- * nor on the optional edge schedule.  Layout: four planes of total_edges doubles {dxl, dyl, dxr, dyr}; boundary and padding
+ * nor on the optional edge schedule.  Layout: four planes of edge_off_plane doubles {dxl, dyl, dxr, dyr}; boundary and padding
  * edges keep 0 (boundary fluxes stay first order, ReconstructFaceValues only visits internal edges). */
 int rdyb_tiled_layout_build_muscl(const RdybLayout *L, RdybTiledLayout *T) {
   RDYB_CHECK(L && T && T->tile_desc, RDYB_ERR_ARG, "tiled MUSCL layout: NULL argument");
   RDYB_CHECK(L->ell_dxs && L->ell_dys && L->ell_dxn && L->ell_dyn, RDYB_ERR_USER, "tiled MUSCL layout: build the MUSCL slot geometry first");
   free(T->edge_off);
-  const size_t plane = (size_t)T->total_edges, S = (size_t)L->stride;
+  const size_t plane = ((size_t)T->total_edges + 3) & ~(size_t)3, S = (size_t)L->stride;
+  T->edge_off_plane = (int64_t)plane;
   T->edge_off = calloc(4 * (plane > 0 ? plane : 1), sizeof(double));
   if (!T->edge_off) return rdyb_fail(RDYB_ERR_MEM, "tiled MUSCL layout: out of memory (face offsets)");
   for (int32_t t = 0; t < T->num_tiles; ++t) {

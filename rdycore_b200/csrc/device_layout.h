@@ -84,9 +84,11 @@ typedef struct {
    * bit 15 set => the cell is the edge's right cell; 0xFFFF => empty */
   uint16_t *cell_edges;      /* [width*stride], slot-major like the ELL arrays */
   int64_t   total_edges, total_halo;
-  /* second order only (rdyb_tiled_layout_build_muscl, NULL otherwise): [4][total_edges] face offsets per tile edge,
-   * edge midpoint - centroid of the left cell (dxl, dyl) and of the right cell (dxr, dyr) */
+  /* second order only (rdyb_tiled_layout_build_muscl, NULL otherwise): [4][edge_off_plane] face offsets per tile edge,
+   * edge midpoint - centroid of the left cell (dxl, dyl) and of the right cell (dxr, dyr); edge_off_plane = total_edges rounded up
+   * to a multiple of 4, so that a tile's slice of every plane starts 16-byte aligned (bulk copies) */
   double   *edge_off;
+  int64_t   edge_off_plane;
 } RdybTiledLayout;
 
 /* warp-tile layout (kernel "warp", K5): every tile of tile_cells cells is cut into mini-tiles of 32 consecutive cells, one per

@@ -24,6 +24,7 @@
 #include "swe_tiled_fixed.cuh"
 #include "swe_tiled_split.cuh"
 #include "swe_tiled_muscl.cuh"
+#include "swe_tiled_muscl_async.cuh"
 #include "swe_warp.cuh"
 
 static std::atomic<int64_t> g_launches{0};
@@ -374,7 +375,7 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
       RDYB_CALL(ensure_courant_slots(op, op->T.num_tiles + 1));
       if (op->recon && !getenv("RDYB_MUSCL_K1")) { /* second order on the tiled layout (K2M); RDYB_MUSCL_K1 keeps it on K1 */
         RDYB_CALL(rdyb_tiled_layout_build_muscl(&op->L, &op->T));
-        RDYB_CALL(upload(&op->t_edge_off, op->T.edge_off, 4 * (size_t)op->T.total_edges));
+        RDYB_CALL(upload(&op->t_edge_off, op->T.edge_off, 4 * (size_t)op->T.edge_off_plane));
       }
       op->has_tiled = true;
     }
@@ -608,9 +609,14 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     fill_args(op, t, in, out, dt);
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile */
-    op->last_kernel = "swe_tiled_muscl_kernel (K2M, MUSCL) + muscl_gradient_kernel";
     op->courant_arg_tiled = true;
-    RDYB_CALL(tiled_muscl_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));
+    if (getenv("RDYB_MUSCL_ASYNC") && tiled_muscl_async_applicable(op->T, op->t_edge_off)) { /* opt-in until it has run on a B200 (swe_tiled_muscl_async.cuh) */
+      op->last_kernel = "swe_tiled_muscl_async_kernel (K3M, MUSCL) + muscl_gradient_kernel";
+      RDYB_CALL(tiled_muscl_async_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));
+    } else {
+      op->last_kernel = "swe_tiled_muscl_kernel (K2M, MUSCL) + muscl_gradient_kernel";
+      RDYB_CALL(tiled_muscl_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));
+    }
     LAUNCHED();
     CU(cudaGetLastError());
     return RDYB_SUCCESS;

@@ -198,7 +198,7 @@ static inline int tiled_muscl_launch(const TiledDev &d, const RdybTiledLayout &T
   p.cell_edges = d.cell_edges;
   p.tile0 = 0;
   p.max_cells = T.tile_cells; p.max_staged = T.tile_cells + T.max_halo; p.max_edges = T.max_edges;
-  const size_t smem = tiled_muscl_smem(T), plane = (size_t)T.total_edges;
+  const size_t smem = tiled_muscl_smem(T), plane = (size_t)T.edge_off_plane;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
   const int nt = T.num_tiles;
 #define TM(R) (xq ? (euler ? tiled_muscl_launch_t<1, true, R>(p, edge_off, plane, nt, smem, stream) : tiled_muscl_launch_t<1, false, R>(p, edge_off, plane, nt, smem, stream)) \

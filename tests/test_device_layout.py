@@ -29,7 +29,7 @@ class RdybTiledLayout(C.Structure):
                 ("tile_cell_begin", c_i32p), ("tile_desc", c_i32p), ("halo_offsets", c_i32p), ("halo_cells", c_i32p), ("edge_offsets", c_i32p),
                 ("edge_lr", c_u32p), ("edge_bidx", c_i32p), ("edge_id", c_i32p), ("edge_cell", c_i32p),
                 ("edge_sn", c_f64p), ("edge_cn", c_f64p), ("edge_len", c_f64p), ("cell_edges", c_u16p),
-                ("total_edges", C.c_int64), ("total_halo", C.c_int64), ("edge_off", c_f64p)]
+                ("total_edges", C.c_int64), ("total_halo", C.c_int64), ("edge_off", c_f64p), ("edge_off_plane", C.c_int64)]
 
 
 def _np(ptr, n):
@@ -61,10 +61,11 @@ def _check_offsets(case, tile_cells, halo=None):
     try:
         va = case.mesh.view_arrays()
         xc, yc, xm, ym, ecells = va["cell_xc"], va["cell_yc"], va["edge_xm"], va["edge_ym"], va["edge_cell_ids"].reshape(-1, 2)
-        plane = T.total_edges
+        plane, ne = T.edge_off_plane, T.total_edges
+        assert plane % 4 == 0 and 0 <= plane - ne < 4  # every plane starts 16-byte aligned (bulk copies of a tile's slice)
         off = _np(T.edge_off, 4 * plane).reshape(4, plane)
         desc = _np(T.tile_desc, 8 * T.num_tiles).reshape(-1, 8)
-        lr, eid, bidx = _np(T.edge_lr, plane), _np(T.edge_id, plane), _np(T.edge_bidx, plane)
+        lr, eid, bidx = _np(T.edge_lr, ne), _np(T.edge_id, ne), _np(T.edge_bidx, ne)
         halo_cells, d2l = _np(T.halo_cells, T.total_halo), _np(L.dev_to_local, L.n_local)
         n_int = n_bnd = 0
         for cb, ncell, eo, nedge, ho, nhalo, _, _ in desc:
