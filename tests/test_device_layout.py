@@ -156,6 +156,10 @@ def test_tiled_layout_invariants(tile_cells, partitioned, schedule, monkeypatch)
             assert eo % 4 == 0 and ho % 4 == 0 and 0 < ncell <= TC and cb == covered
             covered += ncell
             assert (cb + ncell <= NI) if interior else (cb >= NI)
+            # the producer warps fetch every per-tile slice with bulk copies rounded up to 16 bytes (K3, K4, K6, K3M): the rounded
+            # slices must stay inside the arrays, and start 16-byte aligned for every element size in use (2, 4, 8 bytes)
+            assert cb % 8 == 0 and cb + ((ncell + 7) & ~7) <= S
+            assert eo + ((nedge + 3) & ~3) <= T.total_edges and ho + nhalo <= T.total_halo
             h = halo_cells[ho:ho + nhalo]
             assert np.all(np.diff(h) > 0) and not np.any((h >= cb) & (h < cb + ncell)) and np.all((h >= 0) & (h < L.n_local))
             if interior:
