@@ -104,7 +104,7 @@ def main():
             rel, _, mism = assert_state_close(u_by_gid[sg], u_ref_by_gid[sg], what=f"{world}-rank floodplain")
             assert abs(cmax.item() - oracle.courant()) <= 1e-12 * oracle.courant(), "max Courant number differs"
             print(f"MULTIGPU_PARITY ok ranks={world} p2p={args.p2p} hr={args.hr} kernel={args.kernel} steps={args.steps} max_rel={rel:.2e} wetdry_mismatch={mism} "
-                  f"mass_drift={(m1.item() - m0.item()) / m0.item():.2e} courant={cmax.item():.4f}", flush=True)
+                  f"mass_drift={(m1.item() - m0.item()) / m0.item():.2e} courant={cmax.item():.4f} [{op.kernel_info().split(';')[0]}]", flush=True)
         except AssertionError as exc:
             ok = False
             print(f"MULTIGPU_PARITY FAILED: {exc}", flush=True)
