@@ -244,8 +244,8 @@ void rdyb_exodus_free(RdybExodusMesh *m) {
 static int exodus_side_to_edge(const char *elem_type, int nodes_per_elem, int num_dim, int side) {
   const int shell = strncmp(elem_type, "SHELL", 5) == 0 || strncmp(elem_type, "shell", 5) == 0 ||
                     ((strncmp(elem_type, "TRI", 3) == 0 || strncmp(elem_type, "tri", 3) == 0) && num_dim == 3);
-  const int e = shell ? side - 3 : side - 1;
-  return (e >= 0 && e < nodes_per_elem) ? e : -1;
+  const int64_t e = shell ? (int64_t)side - 3 : (int64_t)side - 1;
+  return (e >= 0 && e < nodes_per_elem) ? (int)e : -1;
 }
 
 static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
@@ -310,9 +310,9 @@ static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
     rc = nc_read_int(f, cv, m->elem_nodes + pos, nel * npe, path);
     if (rc) break;
     for (int64_t k = 0; k < nel * npe; ++k) {
-      const int32_t v = m->elem_nodes[pos + k] - 1; /* Exodus is 1-based */
-      if (v < 0 || v >= nn) { rc = rdyb_fail(RDYB_ERR_USER, "%s: %s refers to node %d of %lld", path, name, v + 1, (long long)nn); break; }
-      m->elem_nodes[pos + k] = v;
+      const int64_t v = (int64_t)m->elem_nodes[pos + k] - 1; /* Exodus is 1-based */
+      if (v < 0 || v >= nn) { rc = rdyb_fail(RDYB_ERR_USER, "%s: %s refers to node %lld of %lld", path, name, (long long)v + 1, (long long)nn); break; }
+      m->elem_nodes[pos + k] = (int32_t)v;
     }
     for (int64_t k = 0; k < nel; ++k) {
       m->elem_offsets[e0 + k] = (int32_t)(pos + k * npe);
@@ -349,9 +349,9 @@ static int exodus_build(const NcFile *f, RdybExodusMesh *m, const char *path) {
       snprintf(name, sizeof(name), "side_ss%lld", (long long)s + 1);
       rc = nc_read_int(f, nc_var(f, name), m->side_edges + o, k, path);
       for (int64_t i = 0; i < k && !rc; ++i) {
-        const int32_t el = m->side_elems[o + i] - 1;
-        if (el < 0 || el >= ne) { rc = rdyb_fail(RDYB_ERR_USER, "%s: side set %lld refers to element %d of %lld", path, (long long)s + 1, el + 1, (long long)ne); break; }
-        m->side_elems[o + i] = el;
+        const int64_t el = (int64_t)m->side_elems[o + i] - 1;
+        if (el < 0 || el >= ne) { rc = rdyb_fail(RDYB_ERR_USER, "%s: side set %lld refers to element %lld of %lld", path, (long long)s + 1, (long long)el + 1, (long long)ne); break; }
+        m->side_elems[o + i] = (int32_t)el;
         m->side_edges[o + i] = exodus_side_to_edge(et8 + 8 * el, m->elem_offsets[el + 1] - m->elem_offsets[el], (int)nd, m->side_edges[o + i]);
       }
     }
