@@ -143,6 +143,10 @@ int rdyb_operator_set_options(RdybOperator op, int courant, int flux_divergence,
  * the cell-centric MUSCL gather; rdyb_operator_kernel_info reports which kernel the last launch ran. */
 int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells);
 
+/* at most `max_ctas` CTAs in the grid of the persistent tile kernels (0 = no cap; env RDYB_MAX_CTAS is the process-wide default).
+ * Tests use it so that on a small mesh every CTA walks many tiles - all pipeline stages, both mbarrier parities - as in the bench. */
+int rdyb_operator_set_max_ctas(RdybOperator op, int32_t max_ctas);
+
 /* ---- operator data (host arrays in the reference's layouts) ---- */
 /* SetOperatorBoundaryValues, src/operator.c:1045-1061: values[num_comp*e + c] -> components [comp_offset, comp_offset+num_comp) */
 int rdyb_operator_set_boundary_values(RdybOperator op, int32_t boundary_index, int32_t comp_offset, int32_t num_comp, int32_t num_edges,
@@ -210,6 +214,9 @@ int rdyb_operator_halo_exchange(RdybOperator op);
 #define RDYB_HALO_BLOB_BYTES 512
 int rdyb_operator_halo_export(RdybOperator op, int32_t rank, void *blob);
 int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_t rank, const void *blobs);
+/* clock64() ticks the in-kernel neighbour waits of this rank took since the last call (sum over the waiting CTAs, longest single
+ * wait); resets the counters.  The scaling diagnostic of bench.py: how much of a step is spent waiting for border cells. */
+int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uint64_t *longest);
 
 /* ---- raw device pointers (for zero-copy binding to VECCUDA / torch tensors) ---- */
 /* which: 0..2 = h,hu,hv current state (length num_local), 3..5 = F (length num_owned) */

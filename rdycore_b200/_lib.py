@@ -96,7 +96,8 @@ OPERATOR_SYMBOLS = [
     "rdyb_operator_get_mass", "rdyb_nccl_unique_id", "rdyb_operator_init_comm", "rdyb_operator_halo_exchange",
     "rdyb_operator_device_pointer", "rdyb_operator_last_kernel_ms", "rdyb_operator_set_kernel", "rdyb_operator_get_field",
     "rdyb_host_alloc", "rdyb_host_free", "rdyb_operator_kernel_info", "rdyb_operator_halo_export", "rdyb_operator_halo_import",
-    "rdyb_operator_set_external_source_aos", "rdyb_operator_get_courant_global",
+    "rdyb_operator_set_external_source_aos", "rdyb_operator_get_courant_global", "rdyb_operator_set_max_ctas",
+    "rdyb_operator_get_wait_cycles",
 ]
 
 _lib = None

@@ -140,6 +140,17 @@ def floodplain(nx=2236, ny=2236, dx=10.0, eta0=18.0, hr=False, px=1, py=1, rank=
         r, height = dam_column
         u0[:, 0] = np.where((xc < r) & (yc < r), np.maximum(u0[:, 0], height - zc), u0[:, 0])
         u0[:, 0] = np.maximum(u0[:, 0], 0.0)
+    u0_ghost = None
+    if px * py > 1:
+        # the same initial state on the ghost cells (a caller that freezes ghosts, e.g. a bounded CPU sample of the mesh, starts from it)
+        n_loc = mesh.num_cells
+        gl = np.setdiff1d(np.arange(n_loc, dtype=np.int64), o2l.astype(np.int64), assume_unique=True)
+        gx, gy = mesh.array("cell_xc")[gl], mesh.array("cell_yc")[gl]
+        gz = mesh.view_arrays()["cell_zc"][gl] if hr else mesh.array("cell_zcen")[gl]
+        u0_ghost = np.zeros((len(gl), 3))
+        u0_ghost[:, 0] = np.maximum(0.0, eta0 - gz)
+        if dam_column is not None:
+            u0_ghost[:, 0] = np.maximum(np.where((gx < dam_column[0]) & (gy < dam_column[0]), np.maximum(u0_ghost[:, 0], dam_column[1] - gz), u0_ghost[:, 0]), 0.0)
     bnd = boundaries_from_predicates(mesh, [])
     # keep only boundary edges whose left cell is owned (the reference builds boundaries per rank the same way)
     if px * py > 1:
@@ -152,4 +163,4 @@ def floodplain(nx=2236, ny=2236, dx=10.0, eta0=18.0, hr=False, px=1, py=1, rank=
         dt = 0.25 * 0.2 * dx / np.sqrt(GRAVITY * hmax)  # Courant ~ amax*L/A*dt with L/A ~ 0.3/dx*10
     cfg = make_config(source_method=source_method, well_balancing=WB_HR if hr else WB_NONE)
     return Case("floodplain_%s_%dx%dx2" % ("hr" if hr else "roe", nx, ny), mesh, cfg, bnd, u0, mann, src, float(dt),
-                info={"px": px, "py": py, "rank": rank, "eta0": eta0, "dx": dx})
+                info={"px": px, "py": py, "rank": rank, "eta0": eta0, "dx": dx, "u0_ghost": u0_ghost})

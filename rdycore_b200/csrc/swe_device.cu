@@ -120,6 +120,9 @@ struct RdybOperator_ {
   WarpDev wd;
   const char *last_kernel = "none";
   bool has_warp = false, warp_used = false; /* warp_used: the last launch ran K5 (not a fallback) */
+  int max_ctas = 0; /* cap on the grid of the persistent kernels (0 = none): rdyb_operator_set_max_ctas */
+  long long p2p_timeout_cycles = 40000000000ll; /* in-kernel / wait-kernel neighbour time-out (~20 s; RDYB_P2P_TIMEOUT_S) */
+  unsigned long long *wait_cycles = nullptr; /* [1] clock64() ticks the producers of this rank spent waiting for neighbours (sum over CTAs) */
   int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3),
                           4 = one 32-cell mini-tile per warp (K5; falls back to K4 / K3), 5 = K4's pipeline with the work split across
                           threads and no producer warp (K6; falls back to K4 / K3) */
@@ -195,6 +198,7 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   if (op->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(op->comm);
   for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]);
   if (op->p2p_flags) cudaFree(op->p2p_flags);
+  if (op->wait_cycles) cudaFree(op->wait_cycles);
   fpush_release(op);
   void *ptrs[] = {op->state[0], op->state[1], op->F, op->src, op->mann, op->fdiv, op->prim, op->inv_area, op->area, op->dzdx, op->dzdy, op->zc,
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
@@ -342,6 +346,15 @@ extern "C" int rdyb_operator_set_options(RdybOperator op, int courant, int flux_
   return RDYB_SUCCESS;
 }
 
+/* at most n CTAs in the grid of the persistent kernels (0 = no cap).  On a small mesh this makes every CTA walk many tiles, i.e.
+ * all pipeline stages and both mbarrier parities: the regime of the 10 M-cell bench, reachable by the parity tests. */
+extern "C" int rdyb_operator_set_max_ctas(RdybOperator op, int32_t n) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  RDYB_CHECK(n >= 0, RDYB_ERR_ARG, "negative CTA cap");
+  op->max_ctas = n;
+  return RDYB_SUCCESS;
+}
+
 static void pipe_release(RdybOperator op);
 /* one Courant slot per tile for the kernels that index them by tile number */
 static int ensure_courant_slots(RdybOperator op, int32_t n) {
@@ -396,6 +409,21 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
   return RDYB_SUCCESS;
 }
 
+
+/* peer-memory halo: a neighbour that did not deliver its border cells before the time-out leaves a status word behind; the step
+ * then ran on stale ghosts, so every call that hands data back to the host fails instead of returning it.  Call after a sync. */
+static int p2p_check_status(RdybOperator op) {
+  if (!op->p2p || !op->p2p_flags) return RDYB_SUCCESS;
+  int status = 0;
+  CU(cudaMemcpy(&status, op->p2p_flags + RDYB_MAX_PEERS, sizeof(int), cudaMemcpyDeviceToHost));
+  if (status) {
+    const int pidx = status - 1;
+    return rdyb_fail(RDYB_ERR_NCCL, "peer-memory halo: neighbour %d (rank %d) did not deliver its border cells in time; the state of this rank is invalid",
+                     pidx, pidx >= 0 && pidx < op->L.num_peers ? op->L.peer_ranks[pidx] : -1);
+  }
+  return RDYB_SUCCESS;
+}
+
 /* ---------------- data setters / getters ---------------- */
 extern "C" int rdyb_operator_set_boundary_values(RdybOperator op, int32_t b, int32_t comp_offset, int32_t num_comp, int32_t num_edges,
                                                  const double *values) {
@@ -446,7 +474,7 @@ static int download_owned_component(RdybOperator op, const double *srcp, double 
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * op->N, cudaMemcpyDeviceToHost, op->stream));
   CU(cudaStreamSynchronize(op->stream));
-  return RDYB_SUCCESS;
+  return p2p_check_status(op);
 }
 /* values[i] -> dst[owned_to_dev[ids[i]]] */
 static int upload_regional(RdybOperator op, int32_t n, const int32_t *ids, const double *values, double *dst) {
@@ -532,7 +560,7 @@ extern "C" int rdyb_operator_get_state(RdybOperator op, double *u_global) {
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(u_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
   CU(cudaStreamSynchronize(op->stream));
-  return RDYB_SUCCESS;
+  return p2p_check_status(op);
 }
 extern "C" int rdyb_operator_get_state_component(RdybOperator op, int32_t component, int32_t num_owned, double *values) {
   RDYB_CHECK(op && values, RDYB_ERR_ARG, "NULL argument");
@@ -552,7 +580,7 @@ extern "C" int rdyb_operator_get_field(RdybOperator op, int32_t which, double *v
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
   CU(cudaStreamSynchronize(op->stream));
-  return RDYB_SUCCESS;
+  return p2p_check_status(op);
 }
 
 /* ---------------- launches ---------------- */
@@ -602,6 +630,7 @@ static void launch_gather(RdybOperator op, const SweArgs &a, int grid) {
 /* one RHS / Euler pass over owned device cells [begin,end) */
 static int launch_cells(RdybOperator op, const double *in, double *out, double dt, bool euler, int32_t begin, int32_t end, int32_t cslot0) {
   if (end <= begin) return RDYB_SUCCESS;
+  tl_rdyb_max_ctas = op->max_ctas;
   op->courant_arg_tiled = false;
   if (op->recon && op->kernel_kind >= 1 && op->has_tiled && begin == 0 && end == op->N && tiled_muscl_applicable(op->T, op->t_edge_off)) {
     /* second order on the tiled layout: every tiled kind runs K2M (one launch over all tiles; the state and gradient halos are complete) */
@@ -638,6 +667,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     const bool interior = end <= op->NI;
     const int mh = interior ? op->T.max_halo_interior : op->T.max_halo, me = interior ? op->T.max_edges_interior : op->T.max_edges;
     FixedWait fw = {op->ptab.num_peers, op->p2p_epoch, op->p2p_flags, reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS)};
+    fw.timeout = op->p2p_timeout_cycles; fw.wait_cycles = op->wait_cycles;
     if (op->wait_in_kernel && op->fpush.active && euler) { /* this launch also sends: the epoch the neighbours wait for next */
       const int buf = out == op->state[1];
       fw.order = op->fpush.order; fw.push_range = op->fpush.range; fw.push_src = op->fpush.src; fw.push_dst = op->fpush.dst[buf]; fw.push_rs = op->fpush.rs;
@@ -778,8 +808,16 @@ extern "C" int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_
   const RdybLayout &L = op->L;
   CU(cudaSetDevice(op->device));
   PeerTable &t = op->ptab;
+  CU(cudaStreamSynchronize(op->stream));
+  for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]); /* a repeated import replaces the earlier mapping */
+  op->p2p_nopened = 0;
+  op->p2p = false;
+  CU(cudaMemsetAsync(op->p2p_flags, 0, sizeof(unsigned int) * (RDYB_MAX_PEERS + 8), op->stream));
+  CU(cudaStreamSynchronize(op->stream));
   memset(&t, 0, sizeof(t));
   t.num_peers = L.num_peers;
+  { const char *env = getenv("RDYB_P2P_TIMEOUT_S"); if (env && atof(env) > 0.0) op->p2p_timeout_cycles = (long long)(atof(env) * 2.0e9); }
+  if (!op->wait_cycles) RDYB_CALL(dalloc(&op->wait_cycles, 2));
   for (int p = 0; p < L.num_peers; ++p) {
     const int r = L.peer_ranks[p];
     RDYB_CHECK(r >= 0 && r < nranks && r != rank, RDYB_ERR_USER, "halo plan names rank %d (of %d) as a neighbour of rank %d", r, nranks, rank);
@@ -794,6 +832,7 @@ extern "C" int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_
     void *ptr[3];
     const cudaIpcMemHandle_t hs[3] = {b.state[0], b.state[1], b.flags};
     for (int k = 0; k < 3; ++k) {
+      RDYB_CHECK(op->p2p_nopened < 3 * RDYB_MAX_PEERS, RDYB_ERR_SUP, "too many peer mappings");
       CU(cudaIpcOpenMemHandle(&ptr[k], hs[k], cudaIpcMemLazyEnablePeerAccess));
       op->p2p_opened[op->p2p_nopened++] = ptr[k];
     }
@@ -858,7 +897,7 @@ static int p2p_fused_build(RdybOperator op) {
 }
 
 static int p2p_wait(RdybOperator op) {
-  halo_wait_kernel<<<1, 32, 0, op->stream>>>(op->p2p_flags, op->ptab.num_peers, op->p2p_epoch, 6000000000ll /* ~3 s */,
+  halo_wait_kernel<<<1, 32, 0, op->stream>>>(op->p2p_flags, op->ptab.num_peers, op->p2p_epoch, op->p2p_timeout_cycles,
                                             reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS));
   LAUNCHED();
   CU(cudaGetLastError());
@@ -868,6 +907,9 @@ static int p2p_wait(RdybOperator op) {
 /* one RHS (or fused Euler) evaluation of `in` into `out`, with the halo exchange of `in` overlapped with the interior cells */
 static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool euler) {
   const bool exchange = op->L.num_peers > 0 && op->comm && !op->ghosts_from_caller;
+  /* a partitioned mesh whose ghosts nobody fills would silently compute on stale values */
+  RDYB_CHECK(op->L.num_peers == 0 || op->comm || op->ghosts_from_caller, RDYB_ERR_USER,
+             "this rank has %d neighbour ranks but no communicator: call rdyb_operator_init_comm (or use rdyb_operator_apply_host, whose u_local carries the ghosts)", op->L.num_peers);
   if (op->recon) {
     /* second order: state halo, gradients of the owned cells, gradient halo (two [3][stride] blocks: d/dx and d/dy, the two
      * passes of CommunicateCellGradients), then the reconstructed fluxes.  No overlap yet: this row is correctness-first. */
@@ -1053,18 +1095,23 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   RDYB_CHECK(nsteps >= 0, RDYB_ERR_ARG, "negative step count");
   CU(cudaSetDevice(op->device));
-  CU(cudaEventRecord(op->ev_t0, op->stream));
   if (op->p2p && nsteps > 0 && !op->recon) {
     /* peer-memory halo: the two state buffers alternate, so a neighbour's push for step s+1 lands in the buffer this rank
-     * does not read during step s, and its counter (raised after its frontier kernel) orders everything else */
+     * does not read during step s, and its counter (raised after its frontier tiles) orders everything else.
+     * Epoch accounting is the same on every path, so that ranks which pick different paths (a rank-local decision: tile shapes,
+     * momentum sources) stay in step: one priming push per call (+1), then +1 after every step, the last one included. */
     RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+    /* the timed region of rdyb_operator_last_kernel_ms starts on the device once every neighbour has primed too: host launch
+     * skew between the ranks stays outside it */
+    RDYB_CALL(p2p_wait(op));
+    CU(cudaEventRecord(op->ev_t0, op->stream));
     /* K4 over the whole range: the wait for the neighbours' border cells happens inside the kernel, before a CTA's first frontier tile */
     SweArgs probe;
     fill_args(op, probe, op->state[0], op->state[1], dt);
     const bool one_launch = op->has_tiled && op->kernel_kind == 3 && op->NI < op->N && !getenv("RDYB_P2P_SPLIT_LAUNCH") &&
                             tiled_fixed_applicable(op->T.tile_cells, op->T.max_halo, op->T.max_edges, probe);
     /* fused push: the kernel of step s also delivers the border cells of step s+1 (and raises epoch + 1), so the loop has no
-     * push kernel at all; the explicit push above only primes the first step of the call */
+     * push kernel at all */
     const bool fused = one_launch && op->L.send_offsets[op->L.num_peers] > 0 && !getenv("RDYB_P2P_NO_FUSED_PUSH");
     if (fused) RDYB_CALL(p2p_fused_build(op));
     for (int32_t s = 0; s < nsteps; ++s) {
@@ -1078,16 +1125,17 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
         RDYB_CALL(rc);
         op->cur ^= 1;
         if (fused) ++op->p2p_epoch; /* raised in the neighbours by the kernel itself */
-        else if (s + 1 < nsteps) RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+        else RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
         continue;
       }
       RDYB_CALL(launch_cells(op, in, out, dt, true, 0, op->NI, 0));                       /* interior cells: no ghost needed */
       RDYB_CALL(p2p_wait(op));                                                          /* neighbours' border cells have landed */
       RDYB_CALL(launch_cells(op, in, out, dt, true, op->NI, op->N, op->ncblocks_interior)); /* frontier cells */
       op->cur ^= 1;
-      if (s + 1 < nsteps) RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
+      RDYB_CALL(p2p_push(op, op->state[op->cur], op->cur));
     }
   } else {
+    CU(cudaEventRecord(op->ev_t0, op->stream));
     for (int32_t s = 0; s < nsteps; ++s) {
       RDYB_CALL(rhs_pass(op, op->state[op->cur], op->state[op->cur ^ 1], dt, true));
       op->cur ^= 1;
@@ -1098,6 +1146,22 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
   return RDYB_SUCCESS;
 }
 
+/* ticks (clock64, ~SM clock) the in-kernel neighbour waits of this rank took since the last call: sum over the waiting CTAs and
+ * the longest single wait; resets the counters (syncs) */
+extern "C" int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uint64_t *longest) {
+  RDYB_CHECK(op && sum && longest, RDYB_ERR_ARG, "NULL argument");
+  *sum = 0; *longest = 0;
+  if (!op->wait_cycles) return RDYB_SUCCESS;
+  CU(cudaSetDevice(op->device));
+  unsigned long long h[2] = {0, 0};
+  CU(cudaMemcpyAsync(h, op->wait_cycles, sizeof(h), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaMemsetAsync(op->wait_cycles, 0, sizeof(h), op->stream));
+  CU(cudaStreamSynchronize(op->stream));
+  *sum = h[0]; *longest = h[1];
+  return RDYB_SUCCESS;
+}
+
+extern "C" int rdyb_operator_reset_diagnostics(RdybOperator op);
 extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   CU(cudaSetDevice(op->device));
@@ -1109,6 +1173,7 @@ extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps
   const double a[4] = {0.0, 0.5, 0.5, 1.0};
   const double bw[4] = {1.0 / 6.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 6.0};
   const int g = grid_for(op->N, 256);
+  CU(cudaEventRecord(op->ev_t0, op->stream));
   for (int32_t s = 0; s < nsteps; ++s) {
     double *U = op->state[op->cur];
     for (int i = 0; i < 4; ++i) {
@@ -1119,6 +1184,9 @@ extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps
         CU(cudaGetLastError());
         Y = op->rk_y;
       }
+      /* OperatorRHSFunction resets the diagnostics in every call (src/rdysetup.c:1136), so after TSSolve they hold the LAST stage's
+       * Courant number only: clear the slots before the final stage of the final step */
+      if (i == 3 && s == nsteps - 1 && op->opt_courant) RDYB_CALL(rdyb_operator_reset_diagnostics(op));
       RDYB_CALL(rhs_pass(op, Y, op->rk_k[i], dt, false));
     }
     rk4_combine_kernel<<<g, 256, 0, op->stream>>>(U, op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], dt * bw[0], dt * bw[1], dt * bw[2],
@@ -1126,6 +1194,8 @@ extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps
     LAUNCHED();
     CU(cudaGetLastError());
   }
+  CU(cudaEventRecord(op->ev_t1, op->stream));
+  op->last_launches = nsteps; /* rdyb_operator_last_kernel_ms: ms per STEP (4 RHS evaluations + stage kernels) */
   return RDYB_SUCCESS;
 }
 
@@ -1134,15 +1204,7 @@ extern "C" int rdyb_operator_synchronize(RdybOperator op) {
   CU(cudaSetDevice(op->device));
   CU(cudaStreamSynchronize(op->comm_stream));
   CU(cudaStreamSynchronize(op->stream));
-  if (op->p2p) {
-    int status = 0;
-    CU(cudaMemcpy(&status, op->p2p_flags + RDYB_MAX_PEERS, sizeof(int), cudaMemcpyDeviceToHost));
-    if (status) {
-      CU(cudaMemset(op->p2p_flags + RDYB_MAX_PEERS, 0, sizeof(int)));
-      return rdyb_fail(RDYB_ERR_NCCL, "peer-memory halo: neighbour %d (rank %d) did not deliver its border cells in time", status - 1, op->L.peer_ranks[status - 1]);
-    }
-  }
-  return RDYB_SUCCESS;
+  return p2p_check_status(op);
 }
 
 /* ---------------- diagnostics ---------------- */
@@ -1162,6 +1224,7 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   CU(cudaMemcpyAsync(v.data(), op->cmax, sizeof(double) * v.size(), cudaMemcpyDeviceToHost, op->stream));
   CU(cudaMemcpyAsync(a.data(), op->carg, sizeof(long long) * a.size(), cudaMemcpyDeviceToHost, op->stream));
   CU(cudaStreamSynchronize(op->stream));
+  RDYB_CALL(p2p_check_status(op));
   d->max_courant_num = 0.0; d->global_edge_id = -1; d->global_cell_id = -1; /* ResetOperatorDiagnostics, src/operator.c:757-768 */
   long long arg = -1;
   for (size_t i = 0; i < v.size(); ++i)
@@ -1210,6 +1273,7 @@ extern "C" int rdyb_operator_get_mass(RdybOperator op, double *mass) {
   double host[1024];
   CU(cudaMemcpyAsync(host, op->partial, sizeof(host), cudaMemcpyDeviceToHost, op->stream));
   CU(cudaStreamSynchronize(op->stream));
+  RDYB_CALL(p2p_check_status(op));
   double s = 0.0;
   for (int i = 0; i < 1024; ++i) s += host[i];
   *mass = s;

@@ -25,7 +25,14 @@ __device__ __forceinline__ double swe_rcp(double a) {
   y = fma(y, e, y);
   return y;
 }
-__device__ __forceinline__ double swe_rsqrt(double a) {
+/* rsqrt.approx.ftz flushes a subnormal argument to +0 and returns +Inf, and a Newton step on Inf gives NaN.  Squared speeds
+ * u*u + v*v DO pass through the subnormal range: the leading edge of a disturbance entering still water decays geometrically
+ * and crosses |u| ~ 1e-162..1e-154 (the reference's sqrt() returns a tiny finite value there).  swe_sqrt therefore returns 0
+ * for every argument below 2^-1000 (true value < 1e-150: an absolute error far below one ulp of anything it is added to or
+ * multiplied into on this path) - the same select the a == 0 case always needed, so the hot path pays nothing. */
+#define RDYB_TINY_ARG 9.3326361850321888e-302 /* 2^-1000 */
+/* 1/sqrt(a) for normal positive a */
+__device__ __forceinline__ double swe_rsqrt_core(double a) {
   double y;
   asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
   const double ha = 0.5 * a;
@@ -35,13 +42,13 @@ __device__ __forceinline__ double swe_rsqrt(double a) {
   y = fma(y, e, y);
   return y;
 }
-/* sqrt(a) for a >= 0 (exactly 0 for a == 0); one Heron correction after a*rsqrt(a) */
+/* sqrt(a) for a >= 0; exactly 0 for a < 2^-1000 (0 and the subnormal range included); one Heron correction after a*rsqrt(a) */
 __device__ __forceinline__ double swe_sqrt(double a) {
-  const double y = swe_rsqrt(a);
+  const double y = swe_rsqrt_core(a);
   double s = a * y;
   const double r = fma(-s, s, a);
   s = fma(r, 0.5 * y, s);
-  return a > 0.0 ? s : 0.0;
+  return a >= RDYB_TINY_ARG ? s : 0.0;
 }
 
 /* a^(-1/3) for normal positive a (depths in [tiny_h, ~1e4]): fp32 MUFU seed exp2(-log2(a)/3) (~2^-21) + two Newton steps
@@ -92,7 +99,7 @@ __device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double v
   const double uhat = (duml * ul + dumr * ur) * rsum;
   const double vhat = (duml * vl + dumr * vr) * rsum;
   const double c2 = 0.5 * g * (hl + hr);
-  const double rchat = swe_rsqrt(c2);
+  const double rchat = swe_rsqrt_core(c2); /* c2 >= g tiny_h / 2: normal */
   const double chat = c2 * rchat;
   const double uperp = uhat * cn + vhat * sn;
   const double dh = hr - hl, du = ur - ul, dv = vr - vl;
@@ -107,8 +114,10 @@ __device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double v
   const double da1 = fmax(0.0, 2.0 * (duperp - dc));
   const double da3 = fmax(0.0, 2.0 * (duperp + dc));
   if (FIX) {
-    if (a1 < da1) a1 = 0.5 * (a1 * a1 * swe_rcp(da1) + da1);
-    if (a3 < da3) a3 = 0.5 * (a3 * a3 * swe_rcp(da3) + da3);
+    /* a subnormal da (rcp.approx.ftz would return Inf, and 0 * Inf = NaN) is clamped to 2^-1000: a < da makes a * a underflow to
+     * exactly 0 there, so the quotient is the 0 the reference's division gives */
+    if (a1 < da1) a1 = 0.5 * (a1 * a1 * swe_rcp(fmax(da1, RDYB_TINY_ARG)) + da1);
+    if (a3 < da3) a3 = 0.5 * (a3 * a3 * swe_rcp(fmax(da3, RDYB_TINY_ARG)) + da3);
     needfix = false;
   } else {
     needfix = (a1 < da1) || (a3 < da3); /* the caller re-evaluates these (rare) edges with FIX = true */

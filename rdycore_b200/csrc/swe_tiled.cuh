@@ -247,9 +247,52 @@ static inline int tiled_dev_upload(const RdybTiledLayout *T, const RdybLayout *L
   return RDYB_SUCCESS;
 }
 
+
+/* ---------------- grid of the persistent kernels (K3, K4, K5, K6, K3M) ----------------
+ * One CTA per resident slot: SMs x CTAs/SM, cached PER DEVICE (cudaFuncSetAttribute and the occupancy are per device; an
+ * operator may be created on any device of the process).  Caps, for experiments and tests:
+ *   RDYB_CTAS_PER_SM=n   fewer resident CTAs per SM;
+ *   rdyb_operator_set_max_ctas(op, n) / RDYB_MAX_CTAS=n   at most n CTAs in total, so that on a small mesh every CTA walks many
+ *   tiles through all pipeline stages and both mbarrier parities - the regime of the 10 M-cell bench (tests/test_gpu_parity.py). */
+#define RDYB_MAX_DEVICES 64
+struct PersistentCache {
+  size_t smem[RDYB_MAX_DEVICES];
+  int bps[RDYB_MAX_DEVICES], sms[RDYB_MAX_DEVICES];
+};
+static thread_local int tl_rdyb_max_ctas = 0; /* the launching operator's cap (launch_cells sets it before every launch) */
+
+template <typename Kern>
+static int persistent_grid(Kern kern, int threads, size_t smem, int ntiles, PersistentCache &c, const char *what, int *grid) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= RDYB_MAX_DEVICES) return rdyb_fail(RDYB_ERR_SUP, "%s: device %d out of the supported range", what, dev);
+  if (c.smem[dev] != smem || c.bps[dev] < 1) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "%s: %zu bytes of shared memory per CTA not available (%s)", what, smem, cudaGetErrorString(e));
+    cudaDeviceGetAttribute(&c.sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c.bps[dev], kern, threads, smem);
+    if (e != cudaSuccess || c.bps[dev] < 1) { c.bps[dev] = 0; return rdyb_fail(RDYB_ERR_CUDA, "%s does not fit on an SM with %zu bytes of shared memory", what, smem); }
+    c.smem[dev] = smem;
+  }
+  const char *env = getenv("RDYB_CTAS_PER_SM");
+  int bps = c.bps[dev];
+  if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
+  int g = c.sms[dev] * bps;
+  int cap = tl_rdyb_max_ctas;
+  const char *envc = getenv("RDYB_MAX_CTAS");
+  if (cap <= 0 && envc && atoi(envc) > 0) cap = atoi(envc);
+  if (cap > 0 && g > cap) g = cap;
+  if (g > ntiles) g = ntiles;
+  *grid = g;
+  return RDYB_SUCCESS;
+}
+
 template <bool HR, int SRC, bool EULER, bool COURANT>
 static int tiled_launch_t(const TiledArgs &p, int ntiles, size_t smem, cudaStream_t stream) {
-  static size_t configured = 0; /* per instantiation */
+  static size_t configured_dev[RDYB_MAX_DEVICES] = {}; /* per instantiation and device */
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  size_t &configured = configured_dev[dev_ >= 0 && dev_ < RDYB_MAX_DEVICES ? dev_ : 0];
   if (smem > 48 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(swe_tiled_kernel<HR, SRC, EULER, COURANT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "tiled kernel: %zu bytes of shared memory per tile not available (%s)", smem, cudaGetErrorString(e));

@@ -304,24 +304,10 @@ __global__ void __launch_bounds__(RDYB_ASYNC_THREADS, 2) swe_tiled_async_kernel(
 /* ---------------- host side ---------------- */
 template <bool HR, int SRC, bool EULER, bool COURANT>
 static int async_launch_t(AsyncArgs &q, int ntiles, size_t smem, cudaStream_t stream) {
-  static size_t configured = 0;
-  static int blocks_per_sm = 0, num_sms = 0;
+  static PersistentCache cache = {};
   auto kern = swe_tiled_async_kernel<HR, SRC, EULER, COURANT>;
-  if (smem != configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "async tile kernel: %zu bytes of shared memory per CTA not available (%s)", smem, cudaGetErrorString(e));
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, RDYB_ASYNC_THREADS, smem);
-    if (e != cudaSuccess || blocks_per_sm < 1) return rdyb_fail(RDYB_ERR_CUDA, "async tile kernel does not fit on an SM with %zu bytes of shared memory", smem);
-    configured = smem;
-  }
-  const char *env = getenv("RDYB_CTAS_PER_SM");
-  int bps = blocks_per_sm;
-  if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
-  int grid = num_sms * bps;
-  if (grid > ntiles) grid = ntiles;
+  int grid = 0;
+  RDYB_CALL(persistent_grid(kern, RDYB_ASYNC_THREADS, smem, ntiles, cache, "async tile kernel", &grid));
   kern<<<grid, RDYB_ASYNC_THREADS, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }

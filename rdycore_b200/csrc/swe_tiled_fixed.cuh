@@ -66,6 +66,8 @@ struct FixedArgs {
   unsigned int wait_epoch = 0;
   const unsigned int *wait_flags = nullptr;
   int *wait_status = nullptr;
+  long long wait_timeout = 40000000000ll;      /* clock64() ticks before a missing neighbour is reported in *wait_status */
+  unsigned long long *wait_cycles = nullptr;   /* [0] += ticks this CTA's producer spent in the wait, [1] = max over CTAs */
   /* fused halo push (Euler step only): when a frontier tile is done, its border cells are stored straight into the neighbours'
    * ghost slots of the buffer this step writes; the CTA that finishes the last frontier tile of the launch raises this rank's
    * counter in every neighbour.  Frontier tiles are then scheduled FIRST (tile_order), so the transfer overlaps the interior
@@ -83,6 +85,32 @@ struct FixedArgs {
 
 template <int NCONS>
 __device__ __forceinline__ void fixed_consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory"); }
+
+
+/* the producer warp of a CTA waits here, once per launch, until every neighbour's counter has reached `epoch` (its border cells
+ * of this step have landed in this rank's ghost slots).  Out of line: it runs once per launch and must not cost the tile loop
+ * registers.  A neighbour that stays away longer than `timeout` ticks is reported in *status (a hung peer must not hang this GPU;
+ * every host getter checks the word). */
+__device__ __noinline__ void fixed_neighbour_wait(const unsigned int *flags, int peers, unsigned int epoch, long long timeout, int *status,
+                                                  unsigned long long *wait_cycles, int lane) {
+  long long spun = 0;
+  if (lane < peers) {
+    const volatile unsigned int *f = flags + lane;
+    const long long t0 = clock64();
+    while ((int)(*f - epoch) < 0) {
+      __nanosleep(100);
+      if (clock64() - t0 > timeout) { atomicExch(status, 1 + lane); break; }
+    }
+    spun = clock64() - t0;
+  }
+  if (wait_cycles) { /* how long the step waited for its neighbours: the scaling diagnostic of bench.py */
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) spun = max(spun, __shfl_xor_sync(0xffffffffu, spun, off));
+    if (lane == 0) { atomicAdd(wait_cycles, (unsigned long long)spun); atomicMax(wait_cycles + 1, (unsigned long long)spun); }
+  }
+  __syncwarp();
+  __threadfence_system();
+}
 
 template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
 __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const FixedArgs q) {
@@ -128,16 +156,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
     for (int it = 0; tile < q.tile_end; tile += G, ++it) {
       const int s = it % NS;
       if (tile >= q.wait_tile && tile < q.wait_tile_end && !waited) { /* halo_wait_kernel, inside the step (swe_kernels.cuh) */
-        if (lane < q.wait_peers) {
-          const volatile unsigned int *f = q.wait_flags + lane;
-          const long long t0 = clock64();
-          while ((int)(*f - q.wait_epoch) < 0) {
-            __nanosleep(100);
-            if (clock64() - t0 > 6000000000ll) { atomicExch(q.wait_status, 1 + lane); break; } /* ~3 s: a hung peer must not hang this GPU */
-          }
-        }
-        __syncwarp();
-        __threadfence_system();
+        fixed_neighbour_wait(q.wait_flags, q.wait_peers, q.wait_epoch, q.wait_timeout, q.wait_status, q.wait_cycles, lane);
         waited = true;
       }
       /* prefetch: descriptor two tiles ahead, halo index list one tile ahead */
@@ -382,25 +401,11 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
 /* ---------------- host side ---------------- */
 template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
 static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
-  static bool configured = false;
-  static int blocks_per_sm = 0, num_sms = 0;
+  static PersistentCache cache = {};
   auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, NS, MINB, HR, SRC, EULER, COURANT>;
   const size_t smem = sizeof(FixedSmem<TC, HM, ME, NS, HR>);
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "fixed tile kernel: %zu bytes of shared memory per CTA not available (%s)", smem, cudaGetErrorString(e));
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NCONS + 32, smem);
-    if (e != cudaSuccess || blocks_per_sm < 1) return rdyb_fail(RDYB_ERR_CUDA, "fixed tile kernel does not fit on an SM with %zu bytes of shared memory", smem);
-    configured = true;
-  }
-  const char *env = getenv("RDYB_CTAS_PER_SM");
-  int bps = blocks_per_sm;
-  if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
-  int grid = num_sms * bps;
-  if (grid > ntiles) grid = ntiles;
+  int grid = 0;
+  RDYB_CALL(persistent_grid(kern, NCONS + 32, smem, ntiles, cache, "fixed tile kernel", &grid));
   kern<<<grid, NCONS + 32, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }
@@ -436,6 +441,8 @@ struct FixedWait {
   unsigned int epoch;
   const unsigned int *flags;
   int *status;
+  long long timeout = 40000000000ll;
+  unsigned long long *wait_cycles = nullptr;
   /* fused push (optional): see FixedArgs */
   const int32_t *order = nullptr; /* launch order with the frontier tiles first */
   const int2 *push_range = nullptr;
@@ -465,6 +472,7 @@ static inline int tiled_fixed_launch(const TiledDev &d, const RdybTiledLayout &T
   if (wait && wait->peers > 0 && !d.order && q.tile_end > T.num_interior_tiles) {
     q.wait_tile = T.num_interior_tiles; q.wait_tile_end = T.num_tiles;
     q.wait_peers = wait->peers; q.wait_epoch = wait->epoch; q.wait_flags = wait->flags; q.wait_status = wait->status;
+    q.wait_timeout = wait->timeout; q.wait_cycles = wait->wait_cycles;
     if (wait->push_src && euler && q.tile_begin == 0 && q.tile_end == T.num_tiles) { /* whole range, frontier tiles first */
       p.tile_order = wait->order;
       q.wait_tile = 0; q.wait_tile_end = T.num_tiles - T.num_interior_tiles;

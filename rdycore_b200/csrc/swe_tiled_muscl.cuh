@@ -176,7 +176,10 @@ static inline bool tiled_muscl_applicable(const RdybTiledLayout &T, const double
 
 template <int SRC, bool EULER, int RECON>
 static int tiled_muscl_launch_t(const TiledArgs &p, const double *edge_off, size_t plane, int ntiles, size_t smem, cudaStream_t stream) {
-  static size_t configured = 0; /* per instantiation */
+  static size_t configured_dev[RDYB_MAX_DEVICES] = {}; /* per instantiation and device */
+  int dev_ = 0;
+  cudaGetDevice(&dev_);
+  size_t &configured = configured_dev[dev_ >= 0 && dev_ < RDYB_MAX_DEVICES ? dev_ : 0];
   if (smem > 48 * 1024 && smem > configured) {
     cudaError_t e = cudaFuncSetAttribute(swe_tiled_muscl_kernel<SRC, EULER, RECON>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "tiled MUSCL kernel: %zu bytes of shared memory per tile not available (%s)", smem, cudaGetErrorString(e));

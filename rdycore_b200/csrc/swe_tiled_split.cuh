@@ -320,25 +320,11 @@ __global__ void __launch_bounds__(NT, 2) swe_tiled_split_kernel(const FixedArgs 
 /* ---------------- host side ---------------- */
 template <int TC, int HM, int ME, int NT, bool HR, int SRC, bool EULER, bool COURANT>
 static int split_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
-  static bool configured = false;
-  static int blocks_per_sm = 0, num_sms = 0;
+  static PersistentCache cache = {};
   auto kern = swe_tiled_split_kernel<TC, HM, ME, NT, HR, SRC, EULER, COURANT>;
   const size_t smem = sizeof(SplitSmem<TC, HM, ME, HR>);
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "split tile kernel: %zu bytes of shared memory per CTA not available (%s)", smem, cudaGetErrorString(e));
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NT, smem);
-    if (e != cudaSuccess || blocks_per_sm < 1) return rdyb_fail(RDYB_ERR_CUDA, "split tile kernel does not fit on an SM with %zu bytes of shared memory", smem);
-    configured = true;
-  }
-  const char *env = getenv("RDYB_CTAS_PER_SM");
-  int bps = blocks_per_sm;
-  if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
-  int grid = num_sms * bps;
-  if (grid > ntiles) grid = ntiles;
+  int grid = 0;
+  RDYB_CALL(persistent_grid(kern, NT, smem, ntiles, cache, "split tile kernel", &grid));
   kern<<<grid, NT, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }

@@ -421,27 +421,13 @@ static inline int warp_dev_upload(const RdybWarpLayout *W, const RdybLayout *L, 
 
 template <int TC, int HM, int ME, int WH, int EC, int NS, int NWC, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
 static int warp_launch_t(const WarpArgs &q, int ntiles, cudaStream_t stream) {
-  static bool configured = false;
-  static int blocks_per_sm = 0, num_sms = 0;
+  static PersistentCache cache = {};
   using Smem = WarpSmem<TC, HM, ME, WH, EC, NS, NWC, HR>;
   static_assert(ME % 8 == 0 && WH % 8 == 0 && TC % 64 == 0 && HM % 2 == 0, "bulk-copy alignment of the staged slices");
   auto kern = swe_warp_kernel<TC, HM, ME, WH, EC, NS, NWC, MINB, HR, SRC, EULER, COURANT>;
   const size_t smem = sizeof(Smem);
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "warp tile kernel: %zu bytes of shared memory per CTA not available (%s)", smem, cudaGetErrorString(e));
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, NWC * 32 + 32, smem);
-    if (e != cudaSuccess || blocks_per_sm < 1) return rdyb_fail(RDYB_ERR_CUDA, "warp tile kernel does not fit on an SM with %zu bytes of shared memory", smem);
-    configured = true;
-  }
-  const char *env = getenv("RDYB_CTAS_PER_SM");
-  int bps = blocks_per_sm;
-  if (env && atoi(env) > 0 && atoi(env) < bps) bps = atoi(env);
-  int grid = num_sms * bps;
-  if (grid > ntiles) grid = ntiles;
+  int grid = 0;
+  RDYB_CALL(persistent_grid(kern, NWC * 32 + 32, smem, ntiles, cache, "warp tile kernel", &grid));
   kern<<<grid, NWC * 32 + 32, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }

@@ -58,6 +58,16 @@ class Operator:
     def set_kernel(self, kind: int, tile_cells: int = 512):
         check(lib().rdyb_operator_set_kernel(self._h, C.c_int32(kind), C.c_int32(tile_cells)))
 
+    def set_max_ctas(self, n: int):
+        """Cap the grid of the persistent kernels: every CTA then walks many tiles (the bench regime on a small mesh)."""
+        check(lib().rdyb_operator_set_max_ctas(self._h, C.c_int32(n)))
+
+    def wait_cycles(self):
+        """(sum, longest) clock64 ticks of the in-kernel neighbour waits since the last call."""
+        s, m = C.c_uint64(), C.c_uint64()
+        check(lib().rdyb_operator_get_wait_cycles(self._h, C.byref(s), C.byref(m)))
+        return s.value, m.value
+
     # ---- data ----
     def set_boundary_values(self, boundary_index: int, values, comp_offset: int = 0):
         """values: [num_edges, num_comp] (strided values[num_comp*e + c] as SetOperatorBoundaryValues takes them)."""

@@ -29,6 +29,9 @@ def main():
     ap.add_argument("--kernel", type=int, default=3)
     ap.add_argument("--tile", type=int, default=224)
     ap.add_argument("--p2p", action="store_true", help="peer-memory halo (CUDA IPC over NVLink) instead of NCCL send/recv")
+    ap.add_argument("--mixed-paths", action="store_true", help="momentum sources on rank 0's cells only: rank 0 leaves the fused-push K4 path "
+                    "(general kernel + push kernel) while the other ranks stay on it; the epoch accounting must keep them in step")
+    ap.add_argument("--max-ctas", type=int, default=0, help="cap the persistent grid: every CTA walks many tiles (frontier and interior), the bench regime")
     ap.add_argument("--recon", type=int, default=0, help="second order: 1 minmod, 2 no limiter, 3 van Leer (fully wet case; gradients are exchanged too)")
     args = ap.parse_args()
 
@@ -55,9 +58,18 @@ def main():
             g = c.mesh.array("cell_global_ids")[c.mesh.array("owned_to_local")].astype(np.float64)
             c.u0[:, 1] = 0.3 * np.sin(0.37 * g) * c.u0[:, 0]
             c.u0[:, 2] = 0.3 * np.cos(0.23 * g) * c.u0[:, 0]
+    if args.mixed_paths:
+        for c in (part, serial):
+            m = c.mesh
+            o2l = m.array("owned_to_local")
+            g = m.array("cell_global_ids")[o2l].astype(np.float64)
+            xc = m.array("cell_xc")[o2l]
+            c.sources[:, 1] = np.where(xc < 0.25 * args.nx * 10.0 / 1.0, 1e-4 * np.sin(0.37 * g), 0.0)  # inside rank 0's block (px >= 2)
     op = Operator.from_case(part, device=local, halo=part.mesh.halo())
     if args.kernel:
         op.set_kernel(args.kernel, args.tile)
+    if args.max_ctas:
+        op.set_max_ctas(args.max_ctas)
     uid = [Operator.nccl_unique_id() if rank == 0 else None]
     dist.broadcast_object_list(uid, src=0)
     op.init_comm(world, rank, uid[0])
@@ -66,7 +78,10 @@ def main():
         dist.all_gather_object(blobs, op.halo_export(rank))
         op.halo_import(world, rank, blobs)
     m0 = torch.tensor([op.mass()], dtype=torch.float64, device="cuda")
-    op.step_euler(serial.dt, args.steps - 1)
+    # three calls: each one primes the neighbours again, and the epochs of the fused push carry over between calls
+    n1 = (args.steps - 1) // 2
+    op.step_euler(serial.dt, n1)
+    op.step_euler(serial.dt, args.steps - 1 - n1)
     op.reset_diagnostics()  # the oracle's Courant diagnostic covers its last RHS evaluation only
     op.step_euler(serial.dt, 1)
     op.synchronize()
@@ -104,7 +119,9 @@ def main():
             rel, _, mism = assert_state_close(u_by_gid[sg], u_ref_by_gid[sg], what=f"{world}-rank floodplain")
             assert abs(cmax.item() - oracle.courant()) <= 1e-12 * oracle.courant(), "max Courant number differs"
             print(f"MULTIGPU_PARITY ok ranks={world} p2p={args.p2p} hr={args.hr} kernel={args.kernel} steps={args.steps} max_rel={rel:.2e} wetdry_mismatch={mism} "
-                  f"mass_drift={(m1.item() - m0.item()) / m0.item():.2e} courant={cmax.item():.4f} [{op.kernel_info().split(';')[0]}]", flush=True)
+                  f"mass_drift={(m1.item() - m0.item()) / m0.item():.2e} courant={cmax.item():.4f} max_ctas={args.max_ctas} [{op.kernel_info().split(';')[0]}]", flush=True)
+            if args.mixed_paths:
+                assert "K4" not in op.kernel_info(), "rank 0 was expected to leave the K4 path (momentum sources)"
         except AssertionError as exc:
             ok = False
             print(f"MULTIGPU_PARITY FAILED: {exc}", flush=True)

@@ -21,9 +21,29 @@ SPLIT224 = (TILED_SPLIT, 224)  # K6: K4's pipeline, work split across 384 thread
 KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, FIXED224, SPLIT224, WARP, WARP128]
 
 
+PERSISTENT = {TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP}  # kernels whose CTAs loop over tiles (K3, K4, K6, K5)
+_CAP = 0
+
+
+@pytest.fixture(params=[0, 3], ids=["fullgrid", "cap3"], autouse=True)
+def cta_cap(request):
+    """Every test of this module runs twice: with the full persistent grid (on these small meshes: ONE tile per CTA) and with the
+    grid capped at 3 CTAs (rdyb_operator_set_max_ctas), so that each CTA walks >= 15 tiles through every pipeline stage and both
+    mbarrier parities, with the descriptor / halo-index prefetch chain and the zero-flux slot reused - the regime in which the
+    10 M-cell bench runs (~100 tiles per CTA)."""
+    global _CAP
+    _CAP = request.param
+    yield request.param
+    _CAP = 0
+
+
 def _op(case, kernel=GATHER, **opts):
-    op = Operator.from_case(case)
     kernel, tile = kernel if isinstance(kernel, tuple) else (kernel, 256)
+    if _CAP and kernel not in PERSISTENT:
+        pytest.skip("the grid cap only changes the persistent kernels")
+    op = Operator.from_case(case)
+    if _CAP:
+        op.set_max_ctas(_CAP)
     if kernel != GATHER:
         try:
             op.set_kernel(kernel, tile)
@@ -301,7 +321,7 @@ def test_cuda_rhs_against_reference_golden_vector():
     golden = np.load(_GOLDEN_NPZ)
     builder, _, _ = _GOLDEN["moving_rhs"]
     case = builder()
-    for kernel in (GATHER, TILED_ASYNC):  # 3-component sources: the generic kernels
+    for kernel in ((TILED_ASYNC,) if _CAP else (GATHER, TILED_ASYNC)):  # 3-component sources: the generic kernels
         op = _op(case, kernel, courant=True, flux_divergence=True, primitive_variables=True)
         F = op.apply(case.dt)
         F_ref = golden["moving_rhs/rhs"].reshape(-1, 3)

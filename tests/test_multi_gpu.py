@@ -54,6 +54,40 @@ def test_four_ranks_2x2_blocks():
     _run(4, ["--p2p", "--kernel", "3", "--tile", "224", "--nx", "128", "--ny", "96"], 29541)
 
 
+@pytest.mark.parametrize("hr", [False, True], ids=["roe", "hr"])
+def test_two_ranks_fused_push_many_tiles_per_cta(hr):
+    """The fused in-kernel push with the grid capped at 4 CTAs: a CTA owns several frontier tiles AND many interior tiles, so the
+    neighbour wait, the per-tile sends, the device counter and the epoch flag are exercised in the regime of the 10 M-cell bench."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = _run(2, ["--p2p", "--kernel", "3", "--tile", "224", "--nx", "192", "--ny", "128", "--steps", "90", "--max-ctas", "4"] + (["--hr"] if hr else []), 29581 + hr)
+    assert "K4" in out
+
+
+def test_two_ranks_on_different_step_paths_stay_in_step():
+    """the peer-memory step path is a rank-local decision (tile shapes, momentum sources).  Rank 0 gets momentum
+    sources and runs the general kernel + push kernel, rank 1 the fused-push K4; both advance the halo epoch by one priming push
+    per call plus one per step, so three step_euler calls stay consistent."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, ["--p2p", "--kernel", "3", "--tile", "224", "--steps", "80", "--mixed-paths"], 29587)
+
+
+def test_four_ranks_fused_push_many_tiles_per_cta():
+    if _ngpus() < 4:
+        pytest.skip("needs 4 GPUs")
+    _run(4, ["--p2p", "--kernel", "3", "--tile", "224", "--nx", "192", "--ny", "160", "--steps", "90", "--max-ctas", "5"], 29585)
+
+
+@pytest.mark.parametrize("cap", [0, 6], ids=["fullgrid", "cap6"])
+def test_eight_ranks_4x2_blocks(cap):
+    """4 x 2 blocks: inner ranks have three neighbours (two faces and no corner: ghosts are face neighbours only).  The fused push's
+    release / acquire protocol (stores, fence.sys, device counter, epoch flag per neighbour) with the most neighbours the bench uses."""
+    if _ngpus() < 8:
+        pytest.skip("needs 8 GPUs")
+    _run(8, ["--p2p", "--kernel", "3", "--tile", "224", "--nx", "256", "--ny", "128", "--steps", "90"] + (["--max-ctas", str(cap)] if cap else []), 29590 + cap)
+
+
 def test_two_ranks_second_order_exchanges_gradients():
     """MUSCL on a partitioned mesh: the ghost cells' gradients come from their owners (CommunicateCellGradients,
     src/operator_fluxes_ceed.c:1056-1098) over the same halo plan, after the state halo."""

@@ -74,10 +74,14 @@ def test_port_equals_reference_on_the_reference_decks(name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kernel", [(GATHER, 0), (TILED_FIXED, 224), (TILED_FIXED, 256)])
+@pytest.mark.parametrize("kernel", [(GATHER, 0), (TILED_FIXED, 224), (TILED_FIXED, 256), (TILED_FIXED, 224, 3)],
+                         ids=["K1", "K4-224", "K4-256", "K4-224-cap3"])
 @pytest.mark.parametrize("name", sorted(DECKS))
-def test_cuda_path_runs_the_reference_decks(name, kernel):
+def test_cuda_path_runs_the_reference_decks(name, kernel, monkeypatch):
     """RDyCreate(<the deck's physics / numerics / time sections>) -> RDySetup -> RDyAdvance until RDyFinished, against the oracle."""
+    if len(kernel) == 3:  # persistent grid capped at 3 CTAs: every CTA walks many tiles (the bench regime), via the process-wide default
+        monkeypatch.setenv("RDYB_MAX_CTAS", str(kernel[2]))
+        kernel = kernel[:2]
     case = deck_case(name)
     d = DECKS[name]
     oracle = make_oracle(case)
