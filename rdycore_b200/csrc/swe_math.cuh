@@ -83,6 +83,31 @@ __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, d
   }
 }
 
+/* Primitive state of one edge side, computed where the edge needs it (K4's fused variant: no per-cell pass, no u/v/sqrt(h)
+ * scratch, one CTA barrier per tile less): u, v as swe_velocities<false> and sq = sqrt(h), from ONE MUFU seed.  With
+ * y = 1/sqrt(h): sqrt(h) = h y (+ a Heron correction), 1/h = y y (+ one Newton correction), both <= ~1 ulp.  The general
+ * regularised form hu h / (h^2 + h_a^2) is kept for h_a != 0 (a uniform branch). */
+__device__ __forceinline__ void swe_edge_side(double h, double hu, double hv, double tiny_h, double ha2, double &u, double &v, double &sq) {
+  const bool pos = h >= RDYB_TINY_ARG;
+  const double hs = pos ? h : 1.0;
+  const double y = swe_rsqrt_core(hs);
+  double s = hs * y;
+  const double r = fma(-s, s, hs);
+  s = fma(r, 0.5 * y, s);
+  sq = pos ? s : 0.0;
+  double inv;
+  if (ha2 == 0.0) {
+    inv = y * y;
+    const double e = fma(-hs, inv, 1.0);
+    inv = fma(inv, e, inv);
+  } else {
+    inv = hs * swe_rcp(hs * hs + ha2);
+  }
+  const bool wet = !(h < tiny_h);
+  u = wet ? hu * inv : 0.0;
+  v = wet ? hv * inv : 0.0;
+}
+
 /* ComputeSWERoeEigenspectrum + the flux loop of ComputeSWERoeFlux, src/swe/swe_roe_flux_petsc.h:15-81, 108-128.
  * Inputs are (h,u,v,sqrt h) of the left and right state and the edge normal (cn,sn).  At least one of hl,hr must be > 0.
  * Re-association vs the reference: sqrt(g h) = sqrt(g) sqrt(h); chat and 1/chat from one rsqrt; one shared 1/(duml+dumr); the

@@ -37,20 +37,21 @@ struct alignas(128) FixedStage {
 };
 
 /* per-CTA scratch written by the consumers */
-template <int TC, int HM, int ME, bool HR>
+template <int TC, int HM, int ME, bool HR, bool FUSEP>
 struct alignas(16) FixedScratch {
   static constexpr int CS = TC + HM;
-  double u[CS], v[CS], sq[HR ? 2 : CS];
+  /* FUSEP: the primitive state is computed per edge side in phase 2, so there is no per-cell scratch at all */
+  double u[FUSEP ? 2 : CS], v[FUSEP ? 2 : CS], sq[(HR || FUSEP) ? 2 : CS];
   /* the edge fluxes overwrite the edge geometry of the stage in place (esn <- f0, ecn <- f1, elen <- f2: an edge's thread reads
    * its geometry before it writes its flux).  HR: f1, f2 hold momentum flux + pressure correction as seen by the LEFT cell,
    * f1r, f2r as seen by the RIGHT cell */
   double f1r[HR ? ME : 2], f2r[HR ? ME : 2];
 };
 
-template <int TC, int HM, int ME, int NS, bool HR>
+template <int TC, int HM, int ME, int NS, bool HR, bool FUSEP>
 struct FixedSmem {
   FixedStage<TC, HM, ME, HR> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
-  FixedScratch<TC, HM, ME, HR> sc;
+  FixedScratch<TC, HM, ME, HR, FUSEP> sc;
   uint64_t full_bar[NS], empty_bar[NS];
   double wval[16];
   int wargs[16];
@@ -112,10 +113,10 @@ __device__ __noinline__ void fixed_neighbour_wait(const unsigned int *flags, int
   __threadfence_system();
 }
 
-template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT, bool FUSEP>
 __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const FixedArgs q) {
   extern __shared__ __align__(128) char smem_raw[];
-  using Smem = FixedSmem<TC, HM, ME, NS, HR>;
+  using Smem = FixedSmem<TC, HM, ME, NS, HR, FUSEP>;
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const TiledArgs &p = q.t;
   const SweArgs &a = p.a;
@@ -236,15 +237,19 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       mbar_arrive(&S.empty_bar[s]);
       continue;
     }
-    /* ---- phase 1: primitive state of the staged cells: tile cells [0,TC) and halo cells [TC,TC+nhalo) ---- */
-    for (int x = tid; x < TC + nhalo; x += NCONS) {
-      const double h = st.h[x];
-      double u, w;
-      swe_velocities<HR>(h, st.hu[x], st.hv[x], tiny, ha2, u, w);
-      sc.u[x] = u; sc.v[x] = w;
-      if (!HR) sc.sq[x] = swe_sqrt(h);
+    /* ---- phase 1: primitive state of the staged cells: tile cells [0,TC) and halo cells [TC,TC+nhalo) ----
+     * (FUSEP: folded into phase 2 - each edge derives u, v, sqrt(h) of its two sides from one MUFU seed per side, which costs
+     * fewer instructions than this pass + its loads, and removes a pass, a CTA barrier and 7 KB of scratch per CTA) */
+    if (!FUSEP) {
+      for (int x = tid; x < TC + nhalo; x += NCONS) {
+        const double h = st.h[x];
+        double u, w;
+        swe_velocities<HR>(h, st.hu[x], st.hv[x], tiny, ha2, u, w);
+        sc.u[x] = u; sc.v[x] = w;
+        if (!HR) sc.sq[x] = swe_sqrt(h);
+      }
+      fixed_consumer_sync<NCONS>();
     }
-    fixed_consumer_sync<NCONS>();
 
     /* ---- phase 2: one flux per tile edge ---- */
     for (int e = tid; e < nedge; e += NCONS) {
@@ -257,9 +262,14 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       if (r != 0xffff) {
         double hr = st.h[r];
         if (!(hl < tiny && hr < tiny)) {
-          const double ul = sc.u[l], vl = sc.v[l], ur = sc.u[r], vr = sc.v[r];
+          double ul, vl, ur, vr, sql, sqr;
+          if (FUSEP) {
+            if (HR) { swe_velocities<true>(hl, st.hu[l], st.hv[l], tiny, ha2, ul, vl); swe_velocities<true>(hr, st.hu[r], st.hv[r], tiny, ha2, ur, vr); }
+            else { swe_edge_side(hl, st.hu[l], st.hv[l], tiny, ha2, ul, vl, sql); swe_edge_side(hr, st.hu[r], st.hv[r], tiny, ha2, ur, vr, sqr); }
+          } else {
+            ul = sc.u[l]; vl = sc.v[l]; ur = sc.u[r]; vr = sc.v[r];
+          }
           bool do_flux = true;
-          double sql, sqr;
           if (HR) {
             const double zl = st.z[l], zr = st.z[r], zmax = fmax(zl, zr);
             const double hls = fmax(0.0, (hl + zl) - zmax), hrs = fmax(0.0, (hr + zr) - zmax);
@@ -268,7 +278,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
             hl = hls; hr = hrs;
             do_flux = (hls > tiny || hrs > tiny);
             sql = swe_sqrt(hl); sqr = swe_sqrt(hr);
-          } else {
+          } else if (!FUSEP) {
             sql = sc.sq[l]; sqr = sc.sq[r];
           }
           if (do_flux) {
@@ -399,26 +409,37 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
 }
 
 /* ---------------- host side ---------------- */
-template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT, bool FUSEP>
 static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
   static PersistentCache cache = {};
-  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, NS, MINB, HR, SRC, EULER, COURANT>;
-  const size_t smem = sizeof(FixedSmem<TC, HM, ME, NS, HR>);
+  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, NS, MINB, HR, SRC, EULER, COURANT, FUSEP>;
+  const size_t smem = sizeof(FixedSmem<TC, HM, ME, NS, HR, FUSEP>);
   int grid = 0;
   RDYB_CALL(persistent_grid(kern, NCONS + 32, smem, ntiles, cache, "fixed tile kernel", &grid));
   kern<<<grid, NCONS + 32, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }
 
-template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR>
-static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
+/* FUSEP (the default) folds the primitive-state pass into the edge pass; RDYB_K4_PRIM_PASS=1 restores the three-pass kernel (A/B) */
+static inline bool fixed_prim_pass() {
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("RDYB_K4_PRIM_PASS"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, bool FUSEP>
+static int fixed_launch_cfg2(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
 #define FL(SRCv)                                                                                                                   \
-  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, true>(q, nt, stream)                                  \
-                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, false>(q, nt, stream))                                \
-         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, true>(q, nt, stream)                                 \
-                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, false>(q, nt, stream)))
+  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, true, FUSEP>(q, nt, stream)                           \
+                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, false, FUSEP>(q, nt, stream))                         \
+         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, true, FUSEP>(q, nt, stream)                          \
+                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, false, FUSEP>(q, nt, stream)))
   return xq ? FL(1) : FL(0);
 #undef FL
+}
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR>
+static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
+  return fixed_prim_pass() ? fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, false>(q, nt, xq, euler, courant, stream)
+                           : fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, true>(q, nt, xq, euler, courant, stream);
 }
 
 /* the compiled tile shapes: {tile cells, halo capacity, edge capacity (the last entry is the zero flux), consumer threads,

@@ -28,7 +28,7 @@
 template <int TC, int HM, int ME, bool HR>
 struct SplitSmem {
   FixedStage<TC, HM, ME, HR> st[3];
-  FixedScratch<TC, HM, ME, HR> sc;
+  FixedScratch<TC, HM, ME, HR, false> sc;
   alignas(16) int32_t rec[4][RDYB_SPLIT_REC_INTS];
   uint64_t full_bar[3], rec_bar[4];
   double wval[16];
