@@ -14,6 +14,9 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF_LIB = os.path.join(HERE, "_ref", "libswe_oracle_ref.so")
 PORT_LIB = os.path.join(HERE, "libswe_oracle_port.so")
+# NOT an oracle: the reference's driver code with the B200 adapter's factories (oracle/Makefile target `adapter`); the object under
+# test of tests/test_gpu_rdycore_adapter.py, which drives it through this same binding
+ADAPTER_LIB = os.path.join(HERE, "_ref", "libswe_adapter_ref.so")
 
 
 class Courant(C.Structure):
@@ -21,12 +24,12 @@ class Courant(C.Structure):
 
 
 def build(kind: str = "all") -> None:
-    targets = {"all": ["port", "ref"], "port": ["port"], "reference": ["ref"]}[kind]
+    targets = {"all": ["port", "ref"], "port": ["port"], "reference": ["ref"], "adapter": ["adapter"]}[kind]
     subprocess.run(["make", "-C", HERE, *targets], check=True, capture_output=True)
 
 
 def available(kind: str) -> bool:
-    return os.path.exists(REF_LIB if kind == "reference" else PORT_LIB)
+    return os.path.exists({"reference": REF_LIB, "adapter": ADAPTER_LIB}.get(kind, PORT_LIB))
 
 
 _libs: dict = {}
@@ -35,9 +38,9 @@ _libs: dict = {}
 def load(kind: str) -> C.CDLL:
     """kind = 'reference' (the reference's own code, oracle/_ref) or 'port' (restatement)."""
     if kind not in _libs:
-        path = REF_LIB if kind == "reference" else PORT_LIB
+        path = {"reference": REF_LIB, "adapter": ADAPTER_LIB}.get(kind, PORT_LIB)
         if not os.path.exists(path):
-            build("reference" if kind == "reference" else "port")
+            build(kind if kind in ("reference", "adapter") else "port")
         lib = C.CDLL(path, mode=C.RTLD_LOCAL)
         lib.swe_oracle_kind.restype = C.c_char_p
         lib.swe_oracle_array.restype = C.POINTER(C.c_double)

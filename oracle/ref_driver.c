@@ -97,7 +97,25 @@ static void vec_free(Vec v) {
   if (v) { free(v->a); free(v); }
 }
 
+#ifdef RDYB_ORACLE_USE_B200_FACTORIES
+/* the SAME driver with the four factory calls of CreateOperatorSubOperators switched to the B200 adapter
+ * (rdycore_b200/csrc/rdycore_adapter.c, the reference's signatures): oracle/_ref/libswe_adapter_ref.so, kind "adapter".  Everything
+ * else - the Operator struct and its Vecs, PetscOperatorApply / SetField of the reference's src/petsc_operator.c, the four
+ * statements of ApplyPetscOperator - is unchanged, so a test can compare the two libraries array by array. */
+PetscErrorCode CreateB200FluxOperator(RDyConfig *, RDyMesh *, MPI_Comm, PetscInt, RDyBoundary *, RDyCondition *, Vec *, Vec *, Vec *, OperatorDiagnostics *,
+                                      PetscOperator *);
+PetscErrorCode CreateB200FluxHROperator(RDyConfig *, RDyMesh *, PetscInt, RDyBoundary *, RDyCondition *, Vec *, Vec *, Vec *, OperatorDiagnostics *,
+                                        PetscOperator *);
+PetscErrorCode CreateB200SourceOperator(RDyConfig *, RDyMesh *, Vec, Vec, PetscOperator *);
+PetscErrorCode CreateB200SourceHROperator(RDyConfig *, RDyMesh *, Vec, Vec, PetscOperator *);
+#define CreatePetscFluxOperator CreateB200FluxOperator
+#define CreatePetscFluxHROperator CreateB200FluxHROperator
+#define CreatePetscSourceOperator CreateB200SourceOperator
+#define CreatePetscSourceHROperator CreateB200SourceHROperator
+const char *swe_oracle_kind(void) { return "adapter"; }
+#else
 const char *swe_oracle_kind(void) { return "reference"; }
+#endif
 
 int swe_oracle_create(const RdybConfig *cfg, const RdybMeshView *mv, int32_t nb, const RdybBoundaryView *bv, SweOracle *out) {
   SweOracle o = calloc(1, sizeof(*o));
