@@ -450,11 +450,11 @@ def run_b200_arm(args):
     t_host = time.perf_counter() - t_host
     kinfo = op.kernel_info()
     launches = kernel_launch_count() - n0
-    wait_sum, wait_max = op.wait_cycles()
+    wait_sum, wait_max, wait_n = op.wait_cycles()
     clocks = sampler.stop()
     barrier()
     per_rank_ms = gather_ranks(ms_per_step)
-    per_rank_wait = gather_ranks((wait_sum, wait_max))
+    per_rank_wait = gather_ranks((wait_sum, wait_max, wait_n))
     per_rank_clocks = gather_ranks(clocks)
     ms_per_step = max(per_rank_ms)
     value = total_cells * stages / (ms_per_step * 1e-3)
@@ -521,11 +521,12 @@ def run_b200_arm(args):
                 "kernel_info": kinfo, "kernel": kernel_name, "tile_cells": args.tile if kernel != GATHER else None,
                 "courant_diagnostic": not args.no_courant, "setup_s": round(t_setup, 2), "cells_rank0": int(n_owned),
                 "per_rank_ms_per_step": [round(float(x), 5) for x in per_rank_ms],
-                "per_rank_wait_us_per_step": [round(w[0] / sm_clock / max(args.steps, 1), 3) for w in per_rank_wait],
+                "per_rank_mean_wait_us": [round(w[0] / sm_clock / max(w[2], 1), 3) for w in per_rank_wait],
+                "per_rank_waiting_ctas_per_step": [round(w[2] / max(args.steps, 1), 1) for w in per_rank_wait],
                 "per_rank_longest_wait_us": [round(w[1] / sm_clock, 1) for w in per_rank_wait],
                 "per_rank_sm_mhz": [c.get("sm_mhz") for c in per_rank_clocks],
                 "host_enqueue_ms_per_step": round(1e3 * t_host / max(args.steps, 1), 4),
-                "wait_note": "in-kernel neighbour wait of the producer warps that own a frontier tile: clock64 ticks / SM MHz, summed over the waiting CTAs of a rank, per step",
+                "wait_note": "in-kernel neighbour wait: the producer warp of every CTA that owns a frontier tile waits once per step for its neighbours' border cells (concurrently with the other CTAs); mean and longest single wait in us (clock64 ticks / SM MHz)",
             },
         }
         if not args.no_cpu_baseline and world == 1:

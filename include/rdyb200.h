@@ -193,6 +193,21 @@ int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nsteps);
 int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps);
 int rdyb_operator_synchronize(RdybOperator op);
 
+/* ---- one coupling interval on the device: RDyAdvance without a host round trip (src/rdyadvance.c:261-383) ----
+ * rdyb_operator_time_set puts (t, dt) into a device-resident control block.  rdyb_operator_advance_device then enqueues ONE CUDA
+ * graph: a kernel that reduces the Courant slots of the previous interval's last step and applies the adaptive-dt rule
+ * (:303-343; skipped when `adaptive` is 0 or no Courant number exists yet), and a device-side WHILE loop of fused Euler steps -
+ * whole steps of dt, then one shortened step onto t + interval (TS_EXACTFINALTIME_MATCHSTEP) - whose kernels read dt from the
+ * control block.  Nothing waits on the host; rdyb_operator_time_get (and every state getter) synchronises when asked.
+ * Returns RDYB_ERR_SUP without doing anything when the operator has no device-side loop (partitioned mesh, second order, a
+ * kernel other than K1 / K4): the caller then steps with rdyb_operator_step_euler and its own bookkeeping. */
+int rdyb_operator_time_set(RdybOperator op, double t, double dt);
+int rdyb_operator_time_get(RdybOperator op, double *t, double *dt, int64_t *steps, double *last_courant);
+int rdyb_operator_advance_device(RdybOperator op, double interval, int adaptive, double target_courant, double max_increase_factor);
+/* host waits for the device (stream / event synchronisations) this library performed since load: the "zero host syncs per
+ * RDyAdvance" figure of the tests */
+int64_t rdyb_host_sync_count(void);
+
 /* ---- diagnostics: Reset/Update/GetOperatorDiagnostics, src/operator.c:757-768,867-893 ---- */
 int rdyb_operator_reset_diagnostics(RdybOperator op);
 int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics *diags); /* local max since reset (syncs) */
@@ -215,8 +230,8 @@ int rdyb_operator_halo_exchange(RdybOperator op);
 int rdyb_operator_halo_export(RdybOperator op, int32_t rank, void *blob);
 int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_t rank, const void *blobs);
 /* clock64() ticks the in-kernel neighbour waits of this rank took since the last call (sum over the waiting CTAs, longest single
- * wait); resets the counters.  The scaling diagnostic of bench.py: how much of a step is spent waiting for border cells. */
-int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uint64_t *longest);
+ * wait, number of waits = CTAs owning a frontier tile x launches); resets the counters.  The scaling diagnostic of bench.py: how much of a step is spent waiting for border cells. */
+int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uint64_t *longest, uint64_t *waits);
 
 /* ---- raw device pointers (for zero-copy binding to VECCUDA / torch tensors) ---- */
 /* which: 0..2 = h,hu,hv current state (length num_local), 3..5 = F (length num_owned) */

@@ -97,7 +97,7 @@ OPERATOR_SYMBOLS = [
     "rdyb_operator_device_pointer", "rdyb_operator_last_kernel_ms", "rdyb_operator_set_kernel", "rdyb_operator_get_field",
     "rdyb_host_alloc", "rdyb_host_free", "rdyb_operator_kernel_info", "rdyb_operator_halo_export", "rdyb_operator_halo_import",
     "rdyb_operator_set_external_source_aos", "rdyb_operator_get_courant_global", "rdyb_operator_set_max_ctas",
-    "rdyb_operator_get_wait_cycles",
+    "rdyb_operator_get_wait_cycles", "rdyb_operator_time_set", "rdyb_operator_time_get", "rdyb_operator_advance_device", "rdyb_host_sync_count",
 ]
 
 _lib = None
@@ -123,6 +123,8 @@ def lib() -> C.CDLL:
         _lib.rdyb_last_error.restype = C.c_char_p
         if hasattr(_lib, "rdyb_kernel_launch_count"):
             _lib.rdyb_kernel_launch_count.restype = C.c_int64
+        if hasattr(_lib, "rdyb_host_sync_count"):
+            _lib.rdyb_host_sync_count.restype = C.c_int64
     return _lib
 
 

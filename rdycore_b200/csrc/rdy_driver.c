@@ -57,6 +57,11 @@ struct _p_RDy {
   int32_t step;
   int     courant_valid;
   double  last_courant;
+  /* device-side time loop (rdyb_operator_advance_device): when it runs, dt / step / Courant live in device memory and the fields above
+   * are refreshed only when a getter asks (time_refresh) */
+  int     dev_loop;   /* the last RDyAdvance ran on the device: dt, step, last_courant above are stale */
+  int     ctl_stale;  /* the host path (or a restart) changed time / dt: push them to the device before the next device interval */
+  int32_t step_base;  /* step count at the last rdyb_operator_time_set */
 };
 
 static int g_initialized = 0;
@@ -377,11 +382,27 @@ PetscErrorCode RDySetup(RDy rdy) {
   rdy->time = 0.0; rdy->step = 0;
   rdy->dt = to_seconds(rdy->time_step, rdy->unit); /* InitSolver: TSSetTimeStep(config.time.time_step) */
   rdy->courant_valid = 0;
+  rdy->dev_loop = 0; rdy->ctl_stale = 1; rdy->step_base = 0;
   rdy->is_setup = 1;
   return PETSC_SUCCESS;
 }
 
 /* ------------------------------------------------------------------ RDyAdvance (src/rdyadvance.c:261-383) ---- */
+/* dt, step count and the Courant number of the device-side loop -> the host fields (the one place that waits for the device) */
+static int time_refresh(RDy rdy) {
+  if (!rdy->dev_loop) return RDYB_SUCCESS;
+  double  t, dt, courant;
+  int64_t steps;
+  RDYB_CALL(rdyb_operator_time_get(rdy->op, &t, &dt, &steps, &courant));
+  rdy->dt = dt;
+  rdy->step = rdy->step_base + (int32_t)steps;
+  rdy->last_courant = courant;
+  rdy->courant_valid = courant > 0.0;
+  (void)t; /* == rdy->time: every interval ends exactly on the coupling time */
+  rdy->dev_loop = 0;
+  return RDYB_SUCCESS;
+}
+
 static int run_steps(RDy rdy, double dt, int32_t nsteps) {
   if (nsteps <= 0) return RDYB_SUCCESS;
   if (rdy->physics.temporal == RDYB_TEMPORAL_RK4) return rdyb_operator_step_rk4(rdy->op, dt, nsteps);
@@ -393,6 +414,21 @@ PetscErrorCode RDyAdvance(RDy rdy) {
   RDYB_CHECK(rdy->is_setup, RDYB_ERR_USER, "RDySetup has not been called");
   const double interval = to_seconds(rdy->coupling_interval, rdy->unit);
   const double t_end = rdy->time + interval;
+  if (rdy->physics.temporal == RDYB_TEMPORAL_EULER) {
+    /* the whole interval - dt rule, step count, last-step shortening, Courant reduction - as ONE graph launch with a device-side
+     * loop: no host synchronisation per RDyAdvance.  RDYB_ERR_SUP: this configuration has no device loop (partitioned mesh,
+     * second order, a kernel other than K1 / K4); fall through to the host-driven path below. */
+    if (rdy->ctl_stale) {
+      RDYB_CALL(time_refresh(rdy));
+      RDYB_CALL(rdyb_operator_time_set(rdy->op, rdy->time, rdy->dt));
+      rdy->step_base = rdy->step; rdy->ctl_stale = 0;
+    }
+    const int ierr = rdyb_operator_advance_device(rdy->op, interval, rdy->adaptive, rdy->target_courant, rdy->max_increase_factor);
+    if (ierr == RDYB_SUCCESS) { rdy->time = t_end; rdy->dev_loop = 1; return PETSC_SUCCESS; }
+    if (ierr != RDYB_ERR_SUP) return ierr;
+  }
+  RDYB_CALL(time_refresh(rdy));
+  rdy->ctl_stale = 1;
   if (rdy->adaptive && rdy->courant_valid) { /* :303-343 */
     double dt = rdy->dt;
     if (rdy->last_courant < rdy->target_courant) {
@@ -465,6 +501,7 @@ PetscErrorCode RDyB200WriteCheckpoint(RDy rdy, const char *filename_base, PetscI
   int64_t *ids = NULL;
   RDYB_CHECK(u, RDYB_ERR_MEM, "out of memory");
   int ierr = rdyb_operator_get_state(rdy->op, u);
+  if (!ierr) ierr = time_refresh(rdy);
   if (!ierr) ierr = owned_natural_ids(rdy, &ids);
   const RdybCheckpointMetadata md = {.nproc = nproc, .t = rdy->time, .dt = rdy->dt, .step = rdy->step};
   if (!ierr) ierr = rdyb_checkpoint_write(path, &md, num_global_cells, 3, (int32_t)sizeof(PetscInt), rdy->num_owned, ids, u, rank == 0);
@@ -493,6 +530,7 @@ PetscErrorCode RDyB200ReadCheckpoint(RDy rdy, const char *filename, PetscBool re
     rdy->time = reinitialize ? 0.0 : md.t;
     rdy->step = reinitialize ? 0 : md.step;
     rdy->courant_valid = 0;
+    rdy->dev_loop = 0; rdy->ctl_stale = 1;
   }
   free(u);
   free(ids);
@@ -513,11 +551,13 @@ PetscErrorCode RDyGetTime(RDy rdy, RDyTimeUnit unit, PetscReal *time) {
 }
 PetscErrorCode RDyGetTimeStep(RDy rdy, RDyTimeUnit unit, PetscReal *dt) {
   RDYB_CHECK(rdy && dt, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CALL(time_refresh(rdy));
   *dt = from_seconds(rdy->dt, unit);
   return PETSC_SUCCESS;
 }
 PetscErrorCode RDyGetStep(RDy rdy, PetscInt *step) {
   RDYB_CHECK(rdy && step, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CALL(time_refresh(rdy));
   *step = rdy->step;
   return PETSC_SUCCESS;
 }

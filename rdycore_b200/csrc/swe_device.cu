@@ -28,6 +28,9 @@
 #include "swe_warp.cuh"
 
 static std::atomic<int64_t> g_launches{0};
+static std::atomic<int64_t> g_host_syncs{0}; /* host waits for the device (stream / event synchronisations) since load */
+static inline cudaError_t rdyb_stream_sync(cudaStream_t s) { g_host_syncs.fetch_add(1, std::memory_order_relaxed); return cudaStreamSynchronize(s); }
+static inline cudaError_t rdyb_event_sync(cudaEvent_t e) { g_host_syncs.fetch_add(1, std::memory_order_relaxed); return cudaEventSynchronize(e); }
 
 #define CU(call)                                                                                                   \
   do {                                                                                                             \
@@ -120,6 +123,20 @@ struct RdybOperator_ {
   WarpDev wd;
   const char *last_kernel = "none";
   bool has_warp = false, warp_used = false; /* warp_used: the last launch ran K5 (not a fallback) */
+  /* device-side time loop (rdyb_operator_advance_device): control block, its pinned mirror, the instantiated graph */
+  struct {
+    AdvCtl *ctl = nullptr, *mirror = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    cudaEvent_t ev_mirror = nullptr;
+    bool dirty = false;          /* a launched interval has not been reflected in `cur` / the host's view of t, dt yet */
+    /* what the graph was built for: rebuilt when any of it changes */
+    double interval = 0.0, target = 0.0, maxinc = 0.0;
+    int adaptive = -1, kernel_kind = -1, tile_cells = -1, opts = -1, max_ctas = -1;
+    const double *src_sig = nullptr;
+  } adv;
+  const AdvCtl *adv_ctl_arg = nullptr; /* set around the launches captured into the device-side loop: fill_args passes it on */
+  int adv_buf_arg = 0;
   int max_ctas = 0; /* cap on the grid of the persistent kernels (0 = none): rdyb_operator_set_max_ctas */
   long long p2p_timeout_cycles = 40000000000ll; /* in-kernel / wait-kernel neighbour time-out (~20 s; RDYB_P2P_TIMEOUT_S) */
   unsigned long long *wait_cycles = nullptr; /* [1] clock64() ticks the producers of this rank spent waiting for neighbours (sum over CTAs) */
@@ -180,9 +197,12 @@ static int upload(T **p, const T *src, size_t n) {
 }
 
 extern "C" int64_t rdyb_kernel_launch_count(void) { return g_launches.load(); }
+extern "C" int64_t rdyb_host_sync_count(void) { return g_host_syncs.load(); }
 
 static int grid_for(int64_t n, int block) { return (int)((n + block - 1) / block); }
 
+static void adv_release_graph(RdybOperator op);
+static int adv_resolve(RdybOperator op);
 static void fpush_release(RdybOperator op) { /* the send lists depend on the tiling and on the peer table */
   void *fp[] = {op->fpush.range, op->fpush.src, op->fpush.rs, op->fpush.order, op->fpush.dst[0], op->fpush.dst[1], op->fpush.counter};
   for (void *q : fp)
@@ -194,9 +214,13 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   if (!pop || !*pop) return RDYB_SUCCESS;
   RdybOperator op = *pop;
   cudaSetDevice(op->device);
-  if (op->stream) cudaStreamSynchronize(op->stream);
+  if (op->stream) rdyb_stream_sync(op->stream);
   if (op->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(op->comm);
   for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]);
+  adv_release_graph(op);
+  if (op->adv.ctl) cudaFree(op->adv.ctl);
+  if (op->adv.mirror) cudaFreeHost(op->adv.mirror);
+  if (op->adv.ev_mirror) cudaEventDestroy(op->adv.ev_mirror);
   if (op->p2p_flags) cudaFree(op->p2p_flags);
   if (op->wait_cycles) cudaFree(op->wait_cycles);
   fpush_release(op);
@@ -359,7 +383,7 @@ static void pipe_release(RdybOperator op);
 /* one Courant slot per tile for the kernels that index them by tile number */
 static int ensure_courant_slots(RdybOperator op, int32_t n) {
   if (n <= op->ncblocks) return RDYB_SUCCESS;
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   if (op->cmax) cudaFree(op->cmax);
   if (op->carg) cudaFree(op->carg);
   op->cmax = nullptr; op->carg = nullptr;
@@ -440,7 +464,7 @@ extern "C" int rdyb_operator_set_boundary_values(RdybOperator op, int32_t b, int
     for (int32_t e = 0; e < ne; ++e) tmp[e] = values[(size_t)num_comp * e + c];
     CU(cudaMemcpyAsync(op->bval + (size_t)(comp_offset + c) * op->nbe + op->L.b_offsets[b], tmp.data(), sizeof(double) * ne, cudaMemcpyHostToDevice,
                        op->stream));
-    CU(cudaStreamSynchronize(op->stream));
+    CU(rdyb_stream_sync(op->stream));
   }
   return RDYB_SUCCESS;
 }
@@ -455,7 +479,7 @@ extern "C" int rdyb_operator_get_boundary_fluxes(RdybOperator op, int32_t b, int
   const double *srcp = accumulated ? op->bacc : op->bflux;
   for (int32_t c = 0; c < 3; ++c)
     CU(cudaMemcpyAsync(values + (size_t)c * ne, srcp + (size_t)c * op->nbe + op->L.b_offsets[b], sizeof(double) * ne, cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return RDYB_SUCCESS;
 }
 
@@ -465,7 +489,7 @@ static int upload_owned_component(RdybOperator op, const double *values, double 
   gather_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_owned, dst, op->N);
   LAUNCHED();
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return RDYB_SUCCESS;
 }
 static int download_owned_component(RdybOperator op, const double *srcp, double *values) {
@@ -473,7 +497,7 @@ static int download_owned_component(RdybOperator op, const double *srcp, double 
   LAUNCHED();
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * op->N, cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return p2p_check_status(op);
 }
 /* values[i] -> dst[owned_to_dev[ids[i]]] */
@@ -489,7 +513,7 @@ static int upload_regional(RdybOperator op, int32_t n, const int32_t *ids, const
   scatter_kernel<<<grid_for(n, 256), 256, 0, op->stream>>>(op->stage, op->stage_idx, dst, n);
   LAUNCHED();
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return RDYB_SUCCESS;
 }
 
@@ -513,7 +537,7 @@ extern "C" int rdyb_operator_set_external_source_aos(RdybOperator op, int32_t nu
   aos_to_soa_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_owned, op->src, op->N, op->stride);
   LAUNCHED();
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return RDYB_SUCCESS;
 }
 extern "C" int rdyb_operator_get_external_source(RdybOperator op, int32_t component, int32_t num_owned, double *values) {
@@ -545,21 +569,23 @@ extern "C" int rdyb_operator_set_regional_mannings(RdybOperator op, int32_t n, c
 extern "C" int rdyb_operator_set_state(RdybOperator op, const double *u_global) {
   RDYB_CHECK(op && u_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   CU(cudaMemcpyAsync(op->stage, u_global, sizeof(double) * 3 * op->N, cudaMemcpyHostToDevice, op->stream));
   aos_to_soa_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->stage, op->dev_to_owned, op->state[op->cur], op->N, op->stride);
   LAUNCHED();
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return RDYB_SUCCESS;
 }
 extern "C" int rdyb_operator_get_state(RdybOperator op, double *u_global) {
   RDYB_CHECK(op && u_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->state[op->cur], op->dev_to_owned, op->stage, op->N, op->stride);
   LAUNCHED();
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(u_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return p2p_check_status(op);
 }
 extern "C" int rdyb_operator_get_state_component(RdybOperator op, int32_t component, int32_t num_owned, double *values) {
@@ -567,6 +593,7 @@ extern "C" int rdyb_operator_get_state_component(RdybOperator op, int32_t compon
   RDYB_CHECK(component >= 0 && component < 3, RDYB_ERR_USER, "Invalid component: %d", component);
   RDYB_CHECK(num_owned == op->N, RDYB_ERR_USER, "Wrong size (%d) for owned cell data (should be %d)", num_owned, op->N);
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   return download_owned_component(op, op->state[op->cur] + (size_t)component * op->stride, values);
 }
 /* optional output vectors in the reference's AoS owned layout: which = 0 flux_divergence, 1 primitive_variables, 2 F of the last apply */
@@ -579,7 +606,7 @@ extern "C" int rdyb_operator_get_field(RdybOperator op, int32_t which, double *v
   LAUNCHED();
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(values, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return p2p_check_status(op);
 }
 
@@ -598,6 +625,7 @@ static void fill_args(RdybOperator op, SweArgs &a, const double *in, double *out
   a.cmax = nullptr; a.carg = nullptr;
   a.stride = op->stride; a.width = op->width; a.begin = 0; a.end = 0;
   a.grad = op->grad; a.gcx = op->m_gcx; a.gcy = op->m_gcy; a.dxs = op->m_dxs; a.dys = op->m_dys; a.dxn = op->m_dxn; a.dyn = op->m_dyn;
+  a.ctl = op->adv_ctl_arg; a.ctl_buf = op->adv_buf_arg;
   a.dt = dt; a.tiny_h = op->cfg.tiny_h; a.ha2 = op->cfg.h_anuga_regular * op->cfg.h_anuga_regular; a.xq_thr = op->cfg.xq2018_threshold;
 }
 
@@ -766,6 +794,7 @@ extern "C" int rdyb_operator_init_comm(RdybOperator op, int32_t nranks, int32_t 
 extern "C" int rdyb_operator_halo_exchange(RdybOperator op) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   RDYB_CALL(halo_begin(op, op->state[op->cur]));
   RDYB_CALL(halo_end(op));
   return RDYB_SUCCESS;
@@ -807,17 +836,18 @@ extern "C" int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_
   RDYB_CHECK(op->p2p_flags, RDYB_ERR_USER, "rdyb_operator_halo_export must be called before rdyb_operator_halo_import");
   const RdybLayout &L = op->L;
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   PeerTable &t = op->ptab;
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]); /* a repeated import replaces the earlier mapping */
   op->p2p_nopened = 0;
   op->p2p = false;
   CU(cudaMemsetAsync(op->p2p_flags, 0, sizeof(unsigned int) * (RDYB_MAX_PEERS + 8), op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   memset(&t, 0, sizeof(t));
   t.num_peers = L.num_peers;
   { const char *env = getenv("RDYB_P2P_TIMEOUT_S"); if (env && atof(env) > 0.0) op->p2p_timeout_cycles = (long long)(atof(env) * 2.0e9); }
-  if (!op->wait_cycles) RDYB_CALL(dalloc(&op->wait_cycles, 2));
+  if (!op->wait_cycles) RDYB_CALL(dalloc(&op->wait_cycles, 4));
   for (int p = 0; p < L.num_peers; ++p) {
     const int r = L.peer_ranks[p];
     RDYB_CHECK(r >= 0 && r < nranks && r != rank, RDYB_ERR_USER, "halo plan names rank %d (of %d) as a neighbour of rank %d", r, nranks, rank);
@@ -1044,9 +1074,9 @@ static int apply_host_pipelined(RdybOperator op, double dt, const double *u_loca
   ierr = body();
   op->td.order = nullptr; op->td.sub_begin = op->td.sub_end = 0;
   op->comm = saved;
-  cudaStreamSynchronize(P.s_in);
-  cudaStreamSynchronize(op->stream);
-  cudaError_t e = cudaStreamSynchronize(P.s_out);
+  rdyb_stream_sync(P.s_in);
+  rdyb_stream_sync(op->stream);
+  cudaError_t e = rdyb_stream_sync(P.s_out);
   RDYB_CALL(ierr);
   if (e != cudaSuccess) return rdyb_fail(RDYB_ERR_CUDA, "CUDA error in the pipelined host-Vec apply (%s)", cudaGetErrorString(e));
   return RDYB_SUCCESS;
@@ -1055,6 +1085,7 @@ static int apply_host_pipelined(RdybOperator op, double dt, const double *u_loca
 extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double *u_local, double *f_global) {
   RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   if ((op->kernel_kind == 2 || op->kernel_kind == 3 || op->kernel_kind == 5) && op->has_tiled && !op->recon) { /* K3 / K4: chunked, overlapped copies */
     if (!op->pipe.built || op->pipe.tile_cells != op->T.tile_cells) RDYB_CALL(pipe_build(op));
     if (op->pipe.usable) return apply_host_pipelined(op, dt, u_local, f_global);
@@ -1073,20 +1104,21 @@ extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double
   LAUNCHED();
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(f_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   return RDYB_SUCCESS;
 }
 
 extern "C" int rdyb_operator_apply(RdybOperator op, double dt, double *f_global) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   RDYB_CALL(rhs_pass(op, op->state[op->cur], op->F, dt, false));
   if (f_global) {
     soa_to_aos_kernel<<<grid_for(op->N, 256), 256, 0, op->stream>>>(op->F, op->dev_to_owned, op->stage, op->N, op->stride);
     LAUNCHED();
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(f_global, op->stage, sizeof(double) * 3 * op->N, cudaMemcpyDeviceToHost, op->stream));
-    CU(cudaStreamSynchronize(op->stream));
+    CU(rdyb_stream_sync(op->stream));
   }
   return RDYB_SUCCESS;
 }
@@ -1095,6 +1127,7 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   RDYB_CHECK(nsteps >= 0, RDYB_ERR_ARG, "negative step count");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   if (op->p2p && nsteps > 0 && !op->recon) {
     /* peer-memory halo: the two state buffers alternate, so a neighbour's push for step s+1 lands in the buffer this rank
      * does not read during step s, and its counter (raised after its frontier tiles) orders everything else.
@@ -1146,18 +1179,247 @@ extern "C" int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nste
   return RDYB_SUCCESS;
 }
 
-/* ticks (clock64, ~SM clock) the in-kernel neighbour waits of this rank took since the last call: sum over the waiting CTAs and
- * the longest single wait; resets the counters (syncs) */
-extern "C" int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uint64_t *longest) {
-  RDYB_CHECK(op && sum && longest, RDYB_ERR_ARG, "NULL argument");
-  *sum = 0; *longest = 0;
+/* ticks (clock64, ~SM clock) the in-kernel neighbour waits of this rank took since the last call: sum over the waiting CTAs, the
+ * longest single wait and the number of waits (one per CTA that owns a frontier tile, per launch); resets the counters (syncs) */
+extern "C" int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uint64_t *longest, uint64_t *waits) {
+  RDYB_CHECK(op && sum && longest && waits, RDYB_ERR_ARG, "NULL argument");
+  *sum = 0; *longest = 0; *waits = 0;
   if (!op->wait_cycles) return RDYB_SUCCESS;
   CU(cudaSetDevice(op->device));
-  unsigned long long h[2] = {0, 0};
+  unsigned long long h[4] = {0, 0, 0, 0};
   CU(cudaMemcpyAsync(h, op->wait_cycles, sizeof(h), cudaMemcpyDeviceToHost, op->stream));
   CU(cudaMemsetAsync(op->wait_cycles, 0, sizeof(h), op->stream));
-  CU(cudaStreamSynchronize(op->stream));
-  *sum = h[0]; *longest = h[1];
+  CU(rdyb_stream_sync(op->stream));
+  *sum = h[0]; *longest = h[1]; *waits = h[2];
+  return RDYB_SUCCESS;
+}
+
+/* ---------------- device-side time loop: one coupling interval without a host round trip ----------------
+ * RDyAdvance (src/rdyadvance.c:261-383) = [adaptive-dt rule from the last Courant number, :303-343] + TSSolve to the next
+ * coupling time with TS_EXACTFINALTIME_MATCHSTEP + UpdateOperatorDiagnostics (:366-372).  The reference (and round 1 of this
+ * library) needs the Courant number on the HOST to pick dt and the step count - one synchronisation + reduction per interval, a
+ * round trip per step when the coupling interval is one step.  Here the whole interval is ONE CUDA graph launch:
+ *   adv_begin_kernel   reduces the Courant slots the last step left behind, applies the dt rule, splits the interval into nfull
+ *                      steps of dt + one shortened step (the same arithmetic as the host path, so both give the same bits), and
+ *                      arms the loop;
+ *   a WHILE conditional node (cudaGraphCondTypeWhile) whose body is two fused Euler steps, state buffer 0 -> 1 and 1 -> 0; each
+ *                      step kernel reads its dt and its turn from the control block (SweArgs::ctl) and returns at once when it is
+ *                      not its turn; adv_step_kernel after each advances the step counter, picks the next dt, clears the Courant
+ *                      slots before the LAST step (the reference reports the Courant number of the last RHS evaluation only,
+ *                      src/rdysetup.c:1136) and sets the loop condition with cudaGraphSetConditional.
+ * The host learns t, dt, the step count or which state buffer is current only when a getter asks (adv_resolve). */
+__global__ void __launch_bounds__(256) adv_begin_kernel(AdvCtl *ctl, double *cmax, long long *carg, int32_t nslots, double interval, int adaptive,
+                                                         double target, double maxinc, cudaGraphConditionalHandle handle) {
+  __shared__ double red[256];
+  double m = 0.0;
+  for (int i = threadIdx.x; i < nslots; i += 256) m = fmax(m, cmax[i]);
+  red[threadIdx.x] = m;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if (threadIdx.x < off) red[threadIdx.x] = fmax(red[threadIdx.x], red[threadIdx.x + off]);
+    __syncthreads();
+  }
+  __shared__ int total_s;
+  if (threadIdx.x == 0) {
+    const double courant = red[0];
+    if (ctl->steps > 0) { ctl->courant = courant; ctl->courant_valid = courant > 0.0; } /* UpdateOperatorDiagnostics of the previous interval */
+    double dt = ctl->dt;
+    if (adaptive && ctl->courant_valid) { /* src/rdyadvance.c:303-343 */
+      if (ctl->courant < target) {
+        const double factor = fmin(target / ctl->courant, maxinc);
+        dt *= factor;
+        if (dt > interval) dt = interval;
+      } else {
+        dt *= target / ctl->courant;
+      }
+    }
+    ctl->dt = dt;
+    ctl->t_end = ctl->t + interval;
+    const double span = ctl->t_end - ctl->t; /* as the host path forms it (rdy_driver.c): the same bits, hence the same step split */
+    int nfull = (int)floor(span / dt * (1.0 + 1e-14) + 1e-12);
+    if (nfull < 0) nfull = 0;
+    double rest = span - nfull * dt;
+    if (rest < 1e-12 * fmax(span, dt)) rest = 0.0;
+    ctl->nfull = nfull; ctl->rest = rest; ctl->k = 0;
+    ctl->total = nfull + (rest > 0.0 ? 1 : 0);
+    ctl->dt_step = nfull > 0 ? dt : rest;
+    ctl->active = ctl->total > 0;
+    total_s = ctl->total;
+    cudaGraphSetConditional(handle, ctl->active ? 1u : 0u);
+  }
+  __syncthreads();
+  if (total_s == 1) /* the first step is also the last: its Courant number is the one to report */
+    for (int i = threadIdx.x; i < nslots; i += 256) { cmax[i] = 0.0; carg[i] = -1; }
+}
+
+__global__ void __launch_bounds__(256) adv_step_kernel(AdvCtl *ctl, int32_t buf, double *cmax, long long *carg, int32_t nslots,
+                                                        cudaGraphConditionalHandle handle) {
+  __shared__ int clear_s;
+  if (threadIdx.x == 0) {
+    clear_s = 0;
+    if (ctl->active && ctl->cur == buf) { /* the step kernel before this one ran */
+      ctl->cur = buf ^ 1;
+      ctl->steps += 1;
+      const int k = ++ctl->k;
+      if (k >= ctl->total) {
+        ctl->active = 0;
+        ctl->t = ctl->t_end; /* TS_EXACTFINALTIME_MATCHSTEP: the interval ends exactly on the coupling time */
+      } else {
+        ctl->t += ctl->dt_step;
+        ctl->dt_step = k < ctl->nfull ? ctl->dt : ctl->rest;
+        clear_s = (k == ctl->total - 1);
+      }
+    }
+    cudaGraphSetConditional(handle, ctl->active ? 1u : 0u);
+  }
+  __syncthreads();
+  if (clear_s)
+    for (int i = threadIdx.x; i < nslots; i += 256) { cmax[i] = 0.0; carg[i] = -1; }
+}
+
+static void adv_release_graph(RdybOperator op) {
+  if (op->adv.exec) cudaGraphExecDestroy(op->adv.exec);
+  if (op->adv.graph) cudaGraphDestroy(op->adv.graph);
+  op->adv.exec = nullptr; op->adv.graph = nullptr;
+}
+
+/* bring the host's view (which state buffer is current) up to date after device-side intervals; the only place that waits */
+static int adv_resolve(RdybOperator op) {
+  if (!op->adv.dirty) return RDYB_SUCCESS;
+  CU(rdyb_event_sync(op->adv.ev_mirror));
+  op->cur = op->adv.mirror->cur;
+  op->adv.dirty = false;
+  return RDYB_SUCCESS;
+}
+
+static bool adv_kernel_supported(RdybOperator op, double dt_probe) {
+  if (op->recon || op->L.num_peers > 0) return false; /* second order / partitioned meshes: host-driven path */
+  if (op->kernel_kind == 0) return true;            /* K1 */
+  if (op->kernel_kind == 3 && op->has_tiled) {      /* K4, when the mesh fits its compiled shapes and options */
+    SweArgs probe;
+    fill_args(op, probe, op->state[0], op->state[1], dt_probe);
+    return tiled_fixed_applicable(op->T.tile_cells, op->T.max_halo, op->T.max_edges, probe);
+  }
+  return false;
+}
+
+extern "C" int rdyb_operator_time_set(RdybOperator op, double t, double dt) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  RDYB_CHECK(dt > 0.0, RDYB_ERR_USER, "time step must be positive");
+  CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
+  if (!op->adv.ctl) {
+    RDYB_CALL(dalloc(&op->adv.ctl, 1));
+    CU(cudaMallocHost((void **)&op->adv.mirror, sizeof(AdvCtl)));
+    CU(cudaEventCreateWithFlags(&op->adv.ev_mirror, cudaEventDisableTiming));
+  }
+  AdvCtl c;
+  memset(&c, 0, sizeof(c));
+  c.t = t; c.t_end = t; c.dt = dt; c.dt_step = dt; c.cur = op->cur;
+  *op->adv.mirror = c;
+  CU(cudaMemcpyAsync(op->adv.ctl, op->adv.mirror, sizeof(AdvCtl), cudaMemcpyHostToDevice, op->stream));
+  CU(rdyb_stream_sync(op->stream));
+  return RDYB_SUCCESS;
+}
+
+/* t, dt of the next interval's first guess, steps taken, Courant number of the last finished interval's last step (the value the
+ * dt rule will use); waits for the queued intervals */
+extern "C" int rdyb_operator_time_get(RdybOperator op, double *t, double *dt, int64_t *steps, double *courant) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  RDYB_CHECK(op->adv.ctl, RDYB_ERR_USER, "rdyb_operator_time_set has not been called");
+  CU(cudaSetDevice(op->device));
+  CU(cudaMemcpyAsync(op->adv.mirror, op->adv.ctl, sizeof(AdvCtl), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaEventRecord(op->adv.ev_mirror, op->stream));
+  op->adv.dirty = true;
+  RDYB_CALL(adv_resolve(op));
+  RDYB_CALL(p2p_check_status(op));
+  if (t) *t = op->adv.mirror->t;
+  if (dt) *dt = op->adv.mirror->dt;
+  if (steps) *steps = op->adv.mirror->steps;
+  if (courant) *courant = op->adv.mirror->courant;
+  return RDYB_SUCCESS;
+}
+
+/* returns RDYB_ERR_SUP (and does nothing) when this operator's configuration has no device-side loop: the caller falls back to
+ * rdyb_operator_step_euler with host-side bookkeeping */
+extern "C" int rdyb_operator_advance_device(RdybOperator op, double interval, int adaptive, double target_courant, double max_increase_factor) {
+  RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
+  RDYB_CHECK(interval > 0.0, RDYB_ERR_USER, "coupling interval must be positive");
+  RDYB_CHECK(op->adv.ctl, RDYB_ERR_USER, "rdyb_operator_time_set has not been called");
+  CU(cudaSetDevice(op->device));
+  if (!adv_kernel_supported(op, 1.0) || getenv("RDYB_NO_DEVICE_LOOP")) return RDYB_ERR_SUP;
+  const int opts = (op->opt_courant ? 1 : 0) | (op->opt_fdiv ? 2 : 0) | (op->opt_prim ? 4 : 0) | (op->opt_bflux ? 8 : 0) | (op->mom_src ? 16 : 0);
+  auto &A = op->adv;
+  const bool stale = !A.exec || A.interval != interval || A.adaptive != adaptive || A.target != target_courant || A.maxinc != max_increase_factor ||
+                     A.kernel_kind != op->kernel_kind || A.tile_cells != (op->has_tiled ? op->T.tile_cells : 0) || A.opts != opts || A.max_ctas != op->max_ctas;
+  if (stale) {
+    adv_release_graph(op);
+    const bool courant_was = op->opt_courant;
+    op->opt_courant = true; /* the dt rule needs it */
+    /* configure the kernels outside the capture (function attributes, occupancy): both directions once, gated off */
+    AdvCtl off;
+    memset(&off, 0, sizeof(off));
+    off.cur = -1;
+    AdvCtl *gate_off = nullptr;
+    RDYB_CALL(dalloc(&gate_off, 1));
+    CU(cudaMemcpyAsync(gate_off, &off, sizeof(off), cudaMemcpyHostToDevice, op->stream));
+    auto launch_dir = [&](int buf, const AdvCtl *ctl) -> int {
+      op->adv_ctl_arg = ctl; op->adv_buf_arg = buf;
+      const int rc = launch_cells(op, op->state[buf], op->state[buf ^ 1], 0.0, true, 0, op->N, 0);
+      op->adv_ctl_arg = nullptr;
+      return rc;
+    };
+    int rc = launch_dir(0, gate_off);
+    if (!rc) rc = launch_dir(1, gate_off);
+    CU(rdyb_stream_sync(op->stream));
+    cudaFree(gate_off);
+    (void)courant_was;
+    if (rc) return rc;
+    cudaGraph_t g = nullptr;
+    CU(cudaGraphCreate(&g, 0));
+    A.graph = g;
+    cudaGraphConditionalHandle handle;
+    CU(cudaGraphConditionalHandleCreate(&handle, g, 0, 0));
+    /* node 1: the dt rule */
+    CU(cudaStreamBeginCaptureToGraph(op->stream, g, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    adv_begin_kernel<<<1, 256, 0, op->stream>>>(A.ctl, op->cmax, op->carg, op->ncblocks, interval, adaptive, target_courant, max_increase_factor, handle);
+    cudaGraph_t same = nullptr;
+    CU(cudaStreamEndCapture(op->stream, &same));
+    size_t nnodes = 0;
+    CU(cudaGraphGetNodes(g, nullptr, &nnodes));
+    RDYB_CHECK(nnodes == 1, RDYB_ERR_CUDA, "device-side loop: unexpected graph shape (%zu nodes)", nnodes);
+    cudaGraphNode_t begin_node;
+    CU(cudaGraphGetNodes(g, &begin_node, &nnodes));
+    /* node 2: while (active) { step 0->1; bookkeeping; step 1->0; bookkeeping } */
+    cudaGraphNodeParams &cp = *static_cast<cudaGraphNodeParams *>(calloc(1, sizeof(cudaGraphNodeParams))); /* (its default constructor is deleted; a few bytes per graph build) */
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = handle;
+    cp.conditional.type = cudaGraphCondTypeWhile;
+    cp.conditional.size = 1;
+    cudaGraphNode_t cond_node;
+    CU(cudaGraphAddNode(&cond_node, g, &begin_node, 1, &cp));
+    cudaGraph_t body = cp.conditional.phGraph_out[0];
+    CU(cudaStreamBeginCaptureToGraph(op->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    rc = RDYB_SUCCESS;
+    for (int buf = 0; buf < 2 && !rc; ++buf) {
+      rc = launch_dir(buf, A.ctl);
+      adv_step_kernel<<<1, 256, 0, op->stream>>>(A.ctl, buf, op->cmax, op->carg, op->ncblocks, handle);
+    }
+    cudaGraph_t body_same = nullptr;
+    cudaError_t ce = cudaStreamEndCapture(op->stream, &body_same);
+    if (rc) { adv_release_graph(op); return rc; }
+    if (ce != cudaSuccess) { adv_release_graph(op); return rdyb_fail(RDYB_ERR_CUDA, "device-side loop: capture failed (%s)", cudaGetErrorString(ce)); }
+    ce = cudaGraphInstantiate(&A.exec, g, 0);
+    if (ce != cudaSuccess) { adv_release_graph(op); return rdyb_fail(RDYB_ERR_CUDA, "device-side loop: graph instantiation failed (%s)", cudaGetErrorString(ce)); }
+    A.interval = interval; A.adaptive = adaptive; A.target = target_courant; A.maxinc = max_increase_factor;
+    A.kernel_kind = op->kernel_kind; A.tile_cells = op->has_tiled ? op->T.tile_cells : 0; A.opts = opts; A.max_ctas = op->max_ctas;
+  }
+  CU(cudaGraphLaunch(A.exec, op->stream));
+  LAUNCHED();
+  /* keep the pinned mirror fresh without waiting: a getter only has to wait for this copy */
+  CU(cudaMemcpyAsync(A.mirror, A.ctl, sizeof(AdvCtl), cudaMemcpyDeviceToHost, op->stream));
+  CU(cudaEventRecord(A.ev_mirror, op->stream));
+  A.dirty = true;
   return RDYB_SUCCESS;
 }
 
@@ -1165,6 +1427,7 @@ extern "C" int rdyb_operator_reset_diagnostics(RdybOperator op);
 extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   const size_t S = (size_t)op->stride;
   for (int i = 0; i < 4; ++i)
     if (!op->rk_k[i]) RDYB_CALL(dalloc(&op->rk_k[i], 3 * S));
@@ -1202,8 +1465,8 @@ extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps
 extern "C" int rdyb_operator_synchronize(RdybOperator op) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
   CU(cudaSetDevice(op->device));
-  CU(cudaStreamSynchronize(op->comm_stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->comm_stream));
+  CU(rdyb_stream_sync(op->stream));
   return p2p_check_status(op);
 }
 
@@ -1223,7 +1486,7 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   std::vector<long long> a((size_t)op->ncblocks);
   CU(cudaMemcpyAsync(v.data(), op->cmax, sizeof(double) * v.size(), cudaMemcpyDeviceToHost, op->stream));
   CU(cudaMemcpyAsync(a.data(), op->carg, sizeof(long long) * a.size(), cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   RDYB_CALL(p2p_check_status(op));
   d->max_courant_num = 0.0; d->global_edge_id = -1; d->global_cell_id = -1; /* ResetOperatorDiagnostics, src/operator.c:757-768 */
   long long arg = -1;
@@ -1258,7 +1521,7 @@ extern "C" int rdyb_operator_get_courant_global(RdybOperator op, RdybCourantDiag
   NC(g_nccl.AllReduce(scratch, scratch + 1, 1, ncclDouble, ncclMax, op->comm, op->stream));
   double global = 0.0;
   CU(cudaMemcpyAsync(&global, scratch + 1, sizeof(double), cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   if (global != d->max_courant_num) { d->global_edge_id = -1; d->global_cell_id = -1; }
   d->max_courant_num = global;
   return RDYB_SUCCESS;
@@ -1267,12 +1530,13 @@ extern "C" int rdyb_operator_get_courant_global(RdybOperator op, RdybCourantDiag
 extern "C" int rdyb_operator_get_mass(RdybOperator op, double *mass) {
   RDYB_CHECK(op && mass, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
+  RDYB_CALL(adv_resolve(op));
   mass_partial_kernel<<<1024, 256, 0, op->stream>>>(op->state[op->cur], op->area, op->N, op->partial);
   LAUNCHED();
   CU(cudaGetLastError());
   double host[1024];
   CU(cudaMemcpyAsync(host, op->partial, sizeof(host), cudaMemcpyDeviceToHost, op->stream));
-  CU(cudaStreamSynchronize(op->stream));
+  CU(rdyb_stream_sync(op->stream));
   RDYB_CALL(p2p_check_status(op));
   double s = 0.0;
   for (int i = 0; i < 1024; ++i) s += host[i];
@@ -1283,6 +1547,7 @@ extern "C" int rdyb_operator_get_mass(RdybOperator op, double *mass) {
 extern "C" int rdyb_operator_device_pointer(RdybOperator op, int32_t which, void **ptr, int64_t *length) {
   RDYB_CHECK(op && ptr, RDYB_ERR_ARG, "NULL argument");
   RDYB_CHECK(which >= 0 && which < 6, RDYB_ERR_ARG, "unknown array %d", which);
+  RDYB_CALL(adv_resolve(op));
   if (which < 3) { *ptr = op->state[op->cur] + (size_t)which * op->stride; if (length) *length = op->NL; }
   else { *ptr = op->F + (size_t)(which - 3) * op->stride; if (length) *length = op->N; }
   return RDYB_SUCCESS;
@@ -1291,7 +1556,7 @@ extern "C" int rdyb_operator_device_pointer(RdybOperator op, int32_t which, void
 extern "C" int rdyb_operator_last_kernel_ms(RdybOperator op, double *ms_per_launch, int32_t *launches) {
   RDYB_CHECK(op && ms_per_launch, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
-  CU(cudaEventSynchronize(op->ev_t1));
+  CU(rdyb_event_sync(op->ev_t1));
   float ms = 0.f;
   CU(cudaEventElapsedTime(&ms, op->ev_t0, op->ev_t1));
   *ms_per_launch = op->last_launches > 0 ? (double)ms / op->last_launches : 0.0;

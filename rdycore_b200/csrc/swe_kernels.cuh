@@ -21,6 +21,15 @@
 
 #define RDYB_BLOCK 128
 
+/* Device-resident time control of a coupling interval (rdyb_operator_advance_device): the step kernels of the device-side loop
+ * read their time step, their turn (which state buffer is current) and whether the interval is over from here, so that
+ * RDyAdvance needs no host round trip - not for the adaptive-dt rule (src/rdyadvance.c:303-343), not for the step count. */
+struct AdvCtl {
+  double t, t_end, dt, dt_step, rest, courant;
+  long long steps;
+  int nfull, k, total, cur, active, courant_valid;
+};
+
 struct SweArgs {
   /* state in (device order, SoA, length n_local) */
   const double *__restrict__ h, *__restrict__ hu, *__restrict__ hv;
@@ -46,6 +55,10 @@ struct SweArgs {
    * per-slot least-squares weights / face offsets of device_layout.h; all NULL for first order */
   const double *__restrict__ grad;
   const double *__restrict__ gcx, *__restrict__ gcy, *__restrict__ dxs, *__restrict__ dys, *__restrict__ dxn, *__restrict__ dyn;
+  /* device-side loop (K1 and K4 only): when set, dt is ctl->dt_step and the launch is a no-op unless the interval is active and
+   * ctl->cur == ctl_buf (the launch reads state buffer ctl_buf) */
+  const AdvCtl *ctl = nullptr;
+  int32_t ctl_buf = 0;
 };
 
 /* slope limiters of the MUSCL reconstruction, src/operator_fluxes_ceed.c:1100-1132: the extrapolated increment is limited
@@ -103,6 +116,8 @@ __device__ __forceinline__ void courant_block_reduce(double cmax, long long carg
 
 template <bool HR, int SRC, bool EULER, bool COURANT, int RECON = 0>
 __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a) {
+  if (a.ctl && (!a.ctl->active || a.ctl->cur != a.ctl_buf)) return; /* device-side loop: not this launch's turn */
+  const double dt_ = a.ctl ? a.ctl->dt_step : a.dt;
   const int i = a.begin + blockIdx.x * RDYB_BLOCK + threadIdx.x;
   double cmax = 0.0;
   long long carg = -1;
@@ -149,7 +164,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
         swe_velocities<false>(hr, fr[1], fr[2], tiny, a.ha2, ur, vr);
         const RoeFlux f = swe_roe_flux(hl, ul, vl, swe_sqrt(hl), hr, ur, vr, swe_sqrt(hr), sn, cn);
         if (COURANT) {
-          const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * a.dt;
+          const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * dt_;
           if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
         }
         F0 += f.f0 * scale;
@@ -187,7 +202,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
           else { const double sqn = swe_sqrt(hn); sql = left ? sq : sqn; sqr = left ? sqn : sq; }
           const RoeFlux f = swe_roe_flux(hl, ul, vl, sql, hr, ur, vr, sqr, sn, cn);
           if (COURANT) {
-            const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * a.dt; /* amax*L/min(A_l,A_r)*dt */
+            const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * dt_; /* amax*L/min(A_l,A_r)*dt */
             if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
           }
           F0 += f.f0 * scale;
@@ -215,7 +230,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
         if (ok && !(h < tiny && hr < tiny)) {
           f = swe_roe_flux(h, ul, vl, swe_sqrt(h), hr, ur, vr, swe_sqrt(hr), sn, cn);
           if (COURANT) {
-            const double cnum = f.amax * fabs(slen) * ia * a.dt;
+            const double cnum = f.amax * fabs(slen) * ia * dt_;
             if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
           }
           F0 += f.f0 * scale;
@@ -224,7 +239,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
         }
         if (a.bflux) { /* boundary_fluxes and boundary_fluxes_accum += dt*flux, src/swe/swe_petsc.c:623 */
           a.bflux[j] = f.f0; a.bflux[a.nbe + j] = f.f1; a.bflux[2 * a.nbe + j] = f.f2;
-          a.bacc[j] += a.dt * f.f0; a.bacc[a.nbe + j] += a.dt * f.f1; a.bacc[2 * a.nbe + j] += a.dt * f.f2;
+          a.bacc[j] += dt_ * f.f0; a.bacc[a.nbe + j] += dt_ * f.f1; a.bacc[2 * a.nbe + j] += dt_ * f.f2;
         }
       }
     }
@@ -232,7 +247,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
     /* sources */
     double bedx = 0.0, bedy = 0.0, tbx = 0.0, tby = 0.0;
     if (!HR) { bedx = a.dzdx[i] * g * h; bedy = a.dzdy[i] * g * h; }
-    if (h >= tiny) swe_friction<SRC>(h, hu, hv, F1, F2, bedx, bedy, a.mann[i], a.dt, a.xq_thr, tbx, tby);
+    if (h >= tiny) swe_friction<SRC>(h, hu, hv, F1, F2, bedx, bedy, a.mann[i], dt_, a.xq_thr, tbx, tby);
     const double S1 = a.s1 ? a.s1[i] : 0.0, S2 = a.s2 ? a.s2[i] : 0.0;
     F0 += a.s0[i];
     F1 += -bedx - tbx + S1;
@@ -243,9 +258,9 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
       a.prim[i] = h; a.prim[a.stride + i] = wet ? hu * r : 0.0; a.prim[2 * a.stride + i] = wet ? hv * r : 0.0;
     }
     if (EULER) {
-      a.o0[i] = h + a.dt * F0;
-      a.o1[i] = hu + a.dt * F1;
-      a.o2[i] = hv + a.dt * F2;
+      a.o0[i] = h + dt_ * F0;
+      a.o1[i] = hu + dt_ * F1;
+      a.o2[i] = hv + dt_ * F2;
     } else {
       a.o0[i] = F0;
       a.o1[i] = F1;

@@ -34,6 +34,10 @@ struct alignas(128) FixedStage {
   uint32_t elr[ME];
   uint16_t ce[RDYB_ELL_WIDTH][TC];
   int32_t desc[8];
+  /* HR: the edge fluxes as seen by the RIGHT cell (momentum flux + its pressure correction; the left cell's view overwrites the
+   * edge geometry in place).  Per STAGE, not per CTA: with the fused-primitive variant no CTA barrier separates the cell phase of
+   * tile n from the edge phase of tile n+1, so a fast warp writes these while a slow one still sums the previous tile's. */
+  double f1r[HR ? ME : 2], f2r[HR ? ME : 2];
 };
 
 /* per-CTA scratch written by the consumers */
@@ -43,9 +47,8 @@ struct alignas(16) FixedScratch {
   /* FUSEP: the primitive state is computed per edge side in phase 2, so there is no per-cell scratch at all */
   double u[FUSEP ? 2 : CS], v[FUSEP ? 2 : CS], sq[(HR || FUSEP) ? 2 : CS];
   /* the edge fluxes overwrite the edge geometry of the stage in place (esn <- f0, ecn <- f1, elen <- f2: an edge's thread reads
-   * its geometry before it writes its flux).  HR: f1, f2 hold momentum flux + pressure correction as seen by the LEFT cell,
-   * f1r, f2r as seen by the RIGHT cell */
-  double f1r[HR ? ME : 2], f2r[HR ? ME : 2];
+   * its geometry before it writes its flux).  HR: f1, f2 hold momentum flux + pressure correction as seen by the LEFT cell; the
+   * RIGHT cell's view lives in the stage too (FixedStage::f1r, f2r) */
 };
 
 template <int TC, int HM, int ME, int NS, bool HR, bool FUSEP>
@@ -68,7 +71,7 @@ struct FixedArgs {
   const unsigned int *wait_flags = nullptr;
   int *wait_status = nullptr;
   long long wait_timeout = 40000000000ll;      /* clock64() ticks before a missing neighbour is reported in *wait_status */
-  unsigned long long *wait_cycles = nullptr;   /* [0] += ticks this CTA's producer spent in the wait, [1] = max over CTAs */
+  unsigned long long *wait_cycles = nullptr;   /* [0] += ticks this CTA's producer spent in the wait, [1] = max over CTAs, [2] += 1 per waiting CTA */
   /* fused halo push (Euler step only): when a frontier tile is done, its border cells are stored straight into the neighbours'
    * ghost slots of the buffer this step writes; the CTA that finishes the last frontier tile of the launch raises this rank's
    * counter in every neighbour.  Frontier tiles are then scheduled FIRST (tile_order), so the transfer overlaps the interior
@@ -107,7 +110,7 @@ __device__ __noinline__ void fixed_neighbour_wait(const unsigned int *flags, int
   if (wait_cycles) { /* how long the step waited for its neighbours: the scaling diagnostic of bench.py */
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) spun = max(spun, __shfl_xor_sync(0xffffffffu, spun, off));
-    if (lane == 0) { atomicAdd(wait_cycles, (unsigned long long)spun); atomicMax(wait_cycles + 1, (unsigned long long)spun); }
+    if (lane == 0) { atomicAdd(wait_cycles, (unsigned long long)spun); atomicMax(wait_cycles + 1, (unsigned long long)spun); atomicAdd(wait_cycles + 2, 1ull); }
   }
   __syncwarp();
   __threadfence_system();
@@ -120,15 +123,16 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const TiledArgs &p = q.t;
   const SweArgs &a = p.a;
+  if (a.ctl && (!a.ctl->active || a.ctl->cur != a.ctl_buf)) return; /* device-side loop (rdyb_operator_advance_device): not this launch's turn */
   constexpr int HK = (HM + 31) / 32; /* halo indices per producer lane */
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) {
       mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], NCONS);
       /* the zero flux entry that empty cell-edge slots point at (never touched by the bulk copies: nedge <= ME - 2) */
       S.st[s].esn[ME - 1] = 0.0; S.st[s].ecn[ME - 1] = 0.0; S.st[s].elen[ME - 1] = 0.0;
+      if (HR) { S.st[s].f1r[ME - 1] = 0.0; S.st[s].f2r[ME - 1] = 0.0; }
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    if (HR) { S.sc.f1r[ME - 1] = 0.0; S.sc.f2r[ME - 1] = 0.0; }
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -220,7 +224,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
 
   /* ================= consumer warps ================= */
   auto &sc = S.sc;
-  const double g = RDYB_GRAVITY, tiny = a.tiny_h, ha2 = a.ha2, dt = a.dt;
+  const double g = RDYB_GRAVITY, tiny = a.tiny_h, ha2 = a.ha2, dt = a.ctl ? a.ctl->dt_step : a.dt;
   const int tid = threadIdx.x;
   const int width = a.width;
   double cmax = 0.0;
@@ -320,7 +324,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       }
       const double fl1 = f.f1 * len, fl2 = f.f2 * len;
       st.esn[e] = f.f0 * len; st.ecn[e] = fl1 + k1l; st.elen[e] = fl2 + k2l; /* in place of the edge geometry */
-      if (HR) { sc.f1r[e] = fl1 + k1r; sc.f2r[e] = fl2 + k2r; }
+      if (HR) { st.f1r[e] = fl1 + k1r; st.f2r[e] = fl2 + k2r; }
     }
     fixed_consumer_sync<NCONS>();
 
@@ -340,8 +344,8 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
           F0 = fma(st.esn[e], sgn, F0);
           if (HR) {
             const bool right = (ce & 0x8000u) != 0;
-            F1 = fma(right ? sc.f1r[e] : st.ecn[e], sgn, F1);
-            F2 = fma(right ? sc.f2r[e] : st.elen[e], sgn, F2);
+            F1 = fma(right ? st.f1r[e] : st.ecn[e], sgn, F1);
+            F2 = fma(right ? st.f2r[e] : st.elen[e], sgn, F2);
           } else {
             F1 = fma(st.ecn[e], sgn, F1); F2 = fma(st.elen[e], sgn, F2);
           }

@@ -183,7 +183,7 @@ __device__ __forceinline__ void split_edge(Stage &st, Scratch &sc, const TiledAr
   }
   const double fl1 = f.f1 * len, fl2 = f.f2 * len;
   st.esn[e] = f.f0 * len; st.ecn[e] = fl1 + k1l; st.elen[e] = fl2 + k2l; /* in place of the edge geometry */
-  if (HR) { sc.f1r[e] = fl1 + k1r; sc.f2r[e] = fl2 + k2r; }
+  if (HR) { st.f1r[e] = fl1 + k1r; st.f2r[e] = fl2 + k2r; }
 }
 
 /* one tile cell: flux sum in the reference's slot order (branch-free), bed slope, friction, rain, stage update */
@@ -203,8 +203,8 @@ __device__ __forceinline__ void split_cell(const Stage &st, const Scratch &sc, c
       F0 = fma(st.esn[e], sgn, F0);
       if (HR) {
         const bool right = (ce & 0x8000u) != 0;
-        F1 = fma(right ? sc.f1r[e] : st.ecn[e], sgn, F1);
-        F2 = fma(right ? sc.f2r[e] : st.elen[e], sgn, F2);
+        F1 = fma(right ? st.f1r[e] : st.ecn[e], sgn, F1);
+        F2 = fma(right ? st.f2r[e] : st.elen[e], sgn, F2);
       } else {
         F1 = fma(st.ecn[e], sgn, F1); F2 = fma(st.elen[e], sgn, F2);
       }
@@ -246,10 +246,10 @@ __global__ void __launch_bounds__(NT, 2) swe_tiled_split_kernel(const FixedArgs 
       mbar_init(&S.full_bar[s], 1 + RDYB_SPLIT_GATHER_THREADS);
       /* the zero flux entry that empty cell-edge slots point at (never touched by the bulk copies: nedge <= ME - 2) */
       S.st[s].esn[ME - 1] = 0.0; S.st[s].ecn[ME - 1] = 0.0; S.st[s].elen[ME - 1] = 0.0;
+      if (HR) { S.st[s].f1r[ME - 1] = 0.0; S.st[s].f2r[ME - 1] = 0.0; }
     }
     for (int s = 0; s < 4; ++s) mbar_init(&S.rec_bar[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    if (HR) { S.sc.f1r[ME - 1] = 0.0; S.sc.f2r[ME - 1] = 0.0; }
   }
   __syncthreads();
   const size_t rec_bytes = RDYB_SPLIT_REC_INTS * sizeof(int32_t);

@@ -63,10 +63,10 @@ class Operator:
         check(lib().rdyb_operator_set_max_ctas(self._h, C.c_int32(n)))
 
     def wait_cycles(self):
-        """(sum, longest) clock64 ticks of the in-kernel neighbour waits since the last call."""
-        s, m = C.c_uint64(), C.c_uint64()
-        check(lib().rdyb_operator_get_wait_cycles(self._h, C.byref(s), C.byref(m)))
-        return s.value, m.value
+        """(sum, longest, count) of the in-kernel neighbour waits since the last call, in clock64 ticks."""
+        s, m, n = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(lib().rdyb_operator_get_wait_cycles(self._h, C.byref(s), C.byref(m), C.byref(n)))
+        return s.value, m.value, n.value
 
     # ---- data ----
     def set_boundary_values(self, boundary_index: int, values, comp_offset: int = 0):
@@ -153,6 +153,24 @@ class Operator:
     def step_rk4(self, dt: float, nsteps: int = 1):
         check(lib().rdyb_operator_step_rk4(self._h, C.c_double(dt), C.c_int32(nsteps)))
 
+    # ---- device-side time loop ----
+    def time_set(self, t: float, dt: float):
+        check(lib().rdyb_operator_time_set(self._h, C.c_double(t), C.c_double(dt)))
+
+    def time_get(self):
+        """(t, dt, steps, last Courant number) of the device-resident time control; waits for the queued intervals."""
+        t, dt, c, n = C.c_double(), C.c_double(), C.c_double(), C.c_int64()
+        check(lib().rdyb_operator_time_get(self._h, C.byref(t), C.byref(dt), C.byref(n), C.byref(c)))
+        return t.value, dt.value, n.value, c.value
+
+    def advance_device(self, interval: float, adaptive: bool = False, target_courant: float = 0.5, max_increase_factor: float = 1.1) -> bool:
+        """One coupling interval as a single graph launch with a device-side loop; False when this configuration has none."""
+        code = lib().rdyb_operator_advance_device(self._h, C.c_double(interval), int(adaptive), C.c_double(target_courant), C.c_double(max_increase_factor))
+        if code == 56:  # RDYB_ERR_SUP
+            return False
+        check(code)
+        return True
+
     def synchronize(self):
         check(lib().rdyb_operator_synchronize(self._h))
 
@@ -216,6 +234,10 @@ class Operator:
             self.close()
         except Exception:
             pass
+
+
+def host_sync_count() -> int:
+    return int(lib().rdyb_host_sync_count())
 
 
 def kernel_launch_count() -> int:

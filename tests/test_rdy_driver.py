@@ -225,6 +225,57 @@ def test_adaptive_time_step_follows_the_reference_rule():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("kernel", [(0, 0), (3, 224)], ids=["K1", "K4"])
+@pytest.mark.parametrize("deck", ["adaptive.yaml", "dam_break.yaml"])
+def test_device_side_loop_needs_no_host_sync_and_equals_the_host_loop(deck, kernel, monkeypatch):
+    """the adaptive-dt rule (src/rdyadvance.c:303-343), the step count of the interval and the shortened last step
+    run in a device-side loop (one CUDA graph with a WHILE node per RDyAdvance; dt lives in device memory and the step kernels
+    read it through a pointer).  A run of RDyAdvance calls therefore performs NO host synchronisation at all, and gives the same
+    bits, the same dt and the same step count as the host-driven loop (RDYB_NO_DEVICE_LOOP=1), which reads the Courant number
+    back once per interval."""
+    from rdycore_b200.operator import host_sync_count
+
+    case = cases.floodplain(nx=72, ny=56, eta0=40.0)  # fully wet (see test_adaptive_time_step_follows_the_reference_rule)
+    rng = np.random.default_rng(5)
+    case.u0[:, 1] = 0.4 * rng.normal(size=case.u0.shape[0]) * case.u0[:, 0]
+
+    def run(host_loop):
+        if host_loop:
+            monkeypatch.setenv("RDYB_NO_DEVICE_LOOP", "1")
+        else:
+            monkeypatch.delenv("RDYB_NO_DEVICE_LOOP", raising=False)
+        r = rdy.RDy(os.path.join(DECKS, deck))
+        arr, nb = case.boundary_views()
+        r.set_mesh(case.mesh, arr, nb)
+        if kernel[0]:
+            r.set_kernel(*kernel)
+        r.RDySetup()
+        r.RDySetDomainManningsN(case.mannings)
+        r.RDySetDomainWaterSource(case.sources[:, 0])
+        r.RDySetInitialConditions(case.u0)
+        r.RDyAdvance()  # the first interval builds the graph (and may wait while doing so)
+        n0, calls = host_sync_count(), 1
+        while not r.RDyFinished():
+            r.RDyAdvance()
+            calls += 1
+        syncs = host_sync_count() - n0
+        out = (r.state(), r.RDyGetTimeStep(), r.RDyGetStep(), r.RDyGetTime(), r.max_courant_number())
+        r.RDyDestroy()
+        return out, syncs, calls
+
+    dev, dev_syncs, calls = run(False)
+    host, host_syncs, _ = run(True)
+    assert calls >= 4
+    assert dev_syncs == 0, "RDyAdvance on the device-side loop waited for the device"
+    if deck == "adaptive.yaml":
+        assert host_syncs >= calls - 1  # the host loop reads the Courant number back every interval
+    assert np.array_equal(dev[0], host[0])
+    assert dev[1:4] == host[1:4]
+    assert dev[4] == host[4]
+    assert not np.isnan(dev[0]).any() and dev[2] > calls  # several steps per interval
+
+
+@pytest.mark.gpu
 def test_setters_between_advances():
     """E3SM-style coupling: sources, Manning's n and Dirichlet values change between RDyAdvance calls
     (driver/main.c time loop; src/rdydata.c setters)."""
