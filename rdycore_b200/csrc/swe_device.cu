@@ -1226,20 +1226,22 @@ __global__ void __launch_bounds__(256) adv_begin_kernel(AdvCtl *ctl, double *cma
     double dt = ctl->dt;
     if (adaptive && ctl->courant_valid) { /* src/rdyadvance.c:303-343 */
       if (ctl->courant < target) {
-        const double factor = fmin(target / ctl->courant, maxinc);
-        dt *= factor;
+        const double factor = fmin(__ddiv_rn(target, ctl->courant), maxinc);
+        dt = __dmul_rn(dt, factor);
         if (dt > interval) dt = interval;
       } else {
-        dt *= target / ctl->courant;
+        dt = __dmul_rn(dt, __ddiv_rn(target, ctl->courant));
       }
     }
     ctl->dt = dt;
     ctl->t_end = ctl->t + interval;
     const double span = ctl->t_end - ctl->t; /* as the host path forms it (rdy_driver.c): the same bits, hence the same step split */
-    int nfull = (int)floor(span / dt * (1.0 + 1e-14) + 1e-12);
+    /* no FMA contraction here: the host path (gcc, rdy_driver.c) rounds every operation, and one ulp in `rest` is one ulp in the
+     * last step's dt */
+    int nfull = (int)floor(__dadd_rn(__dmul_rn(__ddiv_rn(span, dt), 1.0 + 1e-14), 1e-12));
     if (nfull < 0) nfull = 0;
-    double rest = span - nfull * dt;
-    if (rest < 1e-12 * fmax(span, dt)) rest = 0.0;
+    double rest = __dsub_rn(span, __dmul_rn((double)nfull, dt));
+    if (rest < __dmul_rn(1e-12, fmax(span, dt))) rest = 0.0;
     ctl->nfull = nfull; ctl->rest = rest; ctl->k = 0;
     ctl->total = nfull + (rest > 0.0 ? 1 : 0);
     ctl->dt_step = nfull > 0 ? dt : rest;
@@ -1265,7 +1267,7 @@ __global__ void __launch_bounds__(256) adv_step_kernel(AdvCtl *ctl, int32_t buf,
         ctl->active = 0;
         ctl->t = ctl->t_end; /* TS_EXACTFINALTIME_MATCHSTEP: the interval ends exactly on the coupling time */
       } else {
-        ctl->t += ctl->dt_step;
+        ctl->t = __dadd_rn(ctl->t, ctl->dt_step);
         ctl->dt_step = k < ctl->nfull ? ctl->dt : ctl->rest;
         clear_s = (k == ctl->total - 1);
       }

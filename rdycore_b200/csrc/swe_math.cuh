@@ -228,4 +228,58 @@ __device__ __forceinline__ void swe_friction(double h, double hu, double hv, dou
   }
 }
 
+
+/* The same friction terms in two halves, for kernels that overlap a barrier wait with the part that does not need the flux
+ * divergence (K4): swe_friction_pre runs before the edge fluxes of the tile are complete, swe_friction_post after.  Operation
+ * for operation the arithmetic of swe_friction, so the two forms give the same bits.
+ * METHOD 0: p0 = tb / (1 + dt tb) (the whole nonlinear part).  METHOD 1: p0 = 1/h, p1 = h^(-1/3) (lambda needs the fluxes). */
+template <int METHOD>
+__device__ __forceinline__ void swe_friction_pre(double h, double hu, double hv, double n, double dt, double &p0, double &p1) {
+  const double g = RDYB_GRAVITY;
+  const double rh = swe_rcp(h);
+  const double rc = swe_rcbrt(h); /* h^(-1/3) */
+  if (METHOD == 0) {
+    const double u = hu * rh, v = hv * rh;
+    const double Cd = g * (n * n) * rc;
+    const double vel = swe_sqrt(u * u + v * v);
+    const double tb = Cd * vel * rh;
+    p0 = tb * swe_rcp(1.0 + dt * tb);
+    p1 = 0.0;
+  } else {
+    p0 = rh;
+    p1 = rc;
+  }
+}
+template <int METHOD>
+__device__ __forceinline__ void swe_friction_post(double p0, double p1, double hu, double hv, double Fx, double Fy, double bedx, double bedy, double n,
+                                                  double dt, double xq_thr, double &tbx, double &tby) {
+  const double g = RDYB_GRAVITY;
+  if (METHOD == 0) {
+    tbx = (hu + dt * Fx - dt * bedx) * p0;
+    tby = (hv + dt * Fy - dt * bedy) * p0;
+  } else {
+    const double rh = p0, rc = p1;
+    const double Ax = Fx - bedx, Ay = Fy - bedy;
+    const double mx = hu + Ax * dt, my = hv + Ay * dt;
+    const double rc2 = rc * rc, rc4 = rc2 * rc2; /* h^(-4/3) */
+    const double mxh = mx * rh, myh = my * rh;
+    const double gn2 = g * (n * n);
+    const double lambda = gn2 * rc4 * swe_sqrt(mxh * mxh + myh * myh);
+    double qx, qy;
+    if (dt * lambda < xq_thr) {
+      qx = mx;
+      qy = my;
+    } else {
+      const double s = swe_sqrt(1.0 + 4.0 * dt * lambda);
+      const double rd = -swe_rcp(2.0 * dt * lambda);
+      qx = (mx - mx * s) * rd;
+      qy = (my - my * s) * rd;
+    }
+    const double qmag = swe_sqrt(qx * qx + qy * qy);
+    const double c = gn2 * (rc4 * rc2 * rc) * qmag; /* g n^2 h^(-7/3) |q| */
+    tbx = c * qx;
+    tby = c * qy;
+  }
+}
+
 #endif

@@ -56,6 +56,7 @@ struct FixedSmem {
   FixedStage<TC, HM, ME, HR> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
   FixedScratch<TC, HM, ME, HR, FUSEP> sc;
   uint64_t full_bar[NS], empty_bar[NS];
+  uint64_t flux_bar; /* FUSEP: every consumer thread arrives when its edges of the tile are done (split barrier, see phase 3) */
   double wval[16];
   int wargs[16];
 };
@@ -132,6 +133,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       S.st[s].esn[ME - 1] = 0.0; S.st[s].ecn[ME - 1] = 0.0; S.st[s].elen[ME - 1] = 0.0;
       if (HR) { S.st[s].f1r[ME - 1] = 0.0; S.st[s].f2r[ME - 1] = 0.0; }
     }
+    mbar_init(&S.flux_bar, NCONS);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -326,9 +328,61 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       st.esn[e] = f.f0 * len; st.ecn[e] = fl1 + k1l; st.elen[e] = fl2 + k2l; /* in place of the edge geometry */
       if (HR) { st.f1r[e] = fl1 + k1r; st.f2r[e] = fl2 + k2r; }
     }
+    /* ---- phase 3: per-cell flux sum (branch-free), sources, update ----
+     * FUSEP: the barrier between the edge pass and the cell pass is SPLIT (an mbarrier: arrive now, wait later).  Between the two a
+     * thread does the part of its cell that needs no flux: loads, bed slope and the nonlinear part of the friction term
+     * (swe_friction_pre: reciprocal, cube root, square root - two thirds of the cell's arithmetic).  Warps with one edge sweep
+     * instead of two used to idle at the barrier; now they overlap it with this work, and only the flux sum and the update remain
+     * behind the wait. */
+    static_assert(TC <= NCONS, "one cell per consumer thread");
+    if (FUSEP) {
+      mbar_arrive(&S.flux_bar);
+      const int t = tid;
+      const bool has = t < ncell;
+      const int i = cb + t;
+      double h = 0.0, hu = 0.0, hv = 0.0, ia = 1.0, bedx = 0.0, bedy = 0.0, p0 = 0.0, p1 = 0.0, mann = 0.0, s0v = 0.0;
+      if (has) {
+        h = st.h[t]; hu = st.hu[t]; hv = st.hv[t]; ia = st.ia[t]; mann = st.mann[t]; s0v = st.s0[t];
+        if (!HR) { bedx = st.dzdx[t] * g * h; bedy = st.dzdy[t] * g * h; }
+        if (h >= tiny) swe_friction_pre<SRC>(h, hu, hv, mann, dt, p0, p1);
+      }
+      mbar_wait(&S.flux_bar, it & 1); /* every edge flux of the tile is in shared memory */
+      if (has) {
+        const int ia_hi = __double2hiint(ia), ia_lo = __double2loint(ia);
+        double F0 = 0.0, F1 = 0.0, F2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < RDYB_ELL_WIDTH; ++k) {
+          if (k < width) {
+            const uint32_t ce = st.ce[k][t];
+            const int e = min((int)(ce & 0x7fffu), ME - 1);                  /* empty slot (0xffff) -> the zero flux entry */
+            const int flip = (int)((~ce & 0x8000u) << 16);                   /* left cell: -1/area, right cell: +1/area */
+            const double sgn = __hiloint2double(ia_hi ^ flip, ia_lo);
+            F0 = fma(st.esn[e], sgn, F0);
+            if (HR) {
+              const bool right = (ce & 0x8000u) != 0;
+              F1 = fma(right ? st.f1r[e] : st.ecn[e], sgn, F1);
+              F2 = fma(right ? st.f2r[e] : st.elen[e], sgn, F2);
+            } else {
+              F1 = fma(st.ecn[e], sgn, F1); F2 = fma(st.elen[e], sgn, F2);
+            }
+          }
+        }
+        if (a.fdiv) { a.fdiv[i] = F0; a.fdiv[a.stride + i] = F1; a.fdiv[2 * a.stride + i] = F2; }
+        double tbx = 0.0, tby = 0.0;
+        if (h >= tiny) swe_friction_post<SRC>(p0, p1, hu, hv, F1, F2, bedx, bedy, mann, dt, a.xq_thr, tbx, tby);
+        F0 += s0v;
+        F1 += -bedx - tbx;
+        F2 += -bedy - tby;
+        if (a.prim) {
+          const bool wet = h >= tiny;
+          const double rr = h * swe_rcp(h * h + ha2);
+          a.prim[i] = h; a.prim[a.stride + i] = wet ? hu * rr : 0.0; a.prim[2 * a.stride + i] = wet ? hv * rr : 0.0;
+        }
+        if (EULER) { a.o0[i] = h + dt * F0; a.o1[i] = hu + dt * F1; a.o2[i] = hv + dt * F2; }
+        else { a.o0[i] = F0; a.o1[i] = F1; a.o2[i] = F2; }
+      }
+    } else {
     fixed_consumer_sync<NCONS>();
-
-    /* ---- phase 3: per-cell flux sum (branch-free), sources, update ---- */
     for (int t = tid; t < ncell; t += NCONS) {
       const int i = cb + t;
       const double h = st.h[t], hu = st.hu[t], hv = st.hv[t], ia = st.ia[t];
@@ -365,6 +419,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       }
       if (EULER) { a.o0[i] = h + dt * F0; a.o1[i] = hu + dt * F1; a.o2[i] = hv + dt * F2; }
       else { a.o0[i] = F0; a.o1[i] = F1; a.o2[i] = F2; }
+    }
     }
     if (EULER && q.push_src && tile < q.wait_tile_end) { /* fused halo push of a frontier tile's border cells (uniform per CTA; frontier tiles come first) */
       const int tn = p.tile_order ? __ldg(p.tile_order + tile) : tile;
