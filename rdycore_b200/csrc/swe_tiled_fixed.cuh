@@ -20,12 +20,17 @@
  */
 #ifndef RDYB_SWE_TILED_FIXED_CUH
 #define RDYB_SWE_TILED_FIXED_CUH
+#ifndef RDYB_K4_DEFAULT_PRIM
+#define RDYB_K4_DEFAULT_PRIM 1 /* until the producer-warp variant (2) has been timed on the B200 */
+#endif
 #include "swe_tiled_async.cuh"
 
 /* one pipeline stage: everything the producer copies for one tile */
-template <int TC, int HM, int ME, bool HR>
+template <int TC, int HM, int ME, bool HR, bool PRIMS = false>
 struct alignas(128) FixedStage {
   static constexpr int CS = TC + HM;
+  /* PRIMS (K4 with PM == 2): the primitive state of the staged cells, written by the PRODUCER warp once the stage has landed */
+  double u[PRIMS ? CS : 2], v[PRIMS ? CS : 2], sq[(PRIMS && !HR) ? CS : 2];
   double h[CS], hu[CS], hv[CS], ia[CS];
   double z[HR ? CS : 2];            /* HR: bed elevation of the staged cells */
   double dzdx[HR ? 2 : TC], dzdy[HR ? 2 : TC];
@@ -41,21 +46,27 @@ struct alignas(128) FixedStage {
 };
 
 /* per-CTA scratch written by the consumers */
-template <int TC, int HM, int ME, bool HR, bool FUSEP>
+template <int TC, int HM, int ME, bool HR, bool NOPRIM>
 struct alignas(16) FixedScratch {
   static constexpr int CS = TC + HM;
-  /* FUSEP: the primitive state is computed per edge side in phase 2, so there is no per-cell scratch at all */
-  double u[FUSEP ? 2 : CS], v[FUSEP ? 2 : CS], sq[(HR || FUSEP) ? 2 : CS];
+  /* NOPRIM (PM != 0): the primitive state is computed per edge side in phase 2 or by the producer into the stage: no per-CTA scratch */
+  double u[NOPRIM ? 2 : CS], v[NOPRIM ? 2 : CS], sq[(HR || NOPRIM) ? 2 : CS];
   /* the edge fluxes overwrite the edge geometry of the stage in place (esn <- f0, ecn <- f1, elen <- f2: an edge's thread reads
    * its geometry before it writes its flux).  HR: f1, f2 hold momentum flux + pressure correction as seen by the LEFT cell; the
    * RIGHT cell's view lives in the stage too (FixedStage::f1r, f2r) */
 };
 
-template <int TC, int HM, int ME, int NS, bool HR, bool FUSEP>
+/* PM, where the primitive state (u, v, sqrt h) of the staged cells is computed:
+ *   0  a pass of the consumer warps over the staged cells + a CTA barrier (round 1's three-pass kernel);
+ *   1  per edge side inside the edge pass (no pass, no barrier, but 2 evaluations per edge instead of 1.3 per cell);
+ *   2  by the PRODUCER warp, which is otherwise parked: once per staged cell, into the stage, one tile ahead of the consumers,
+ *      announced through prim_bar - the consumers neither compute it nor wait at a barrier for it.
+ * PM != 0 also splits the barrier between the edge pass and the cell pass (flux_bar, see phase 3). */
+template <int TC, int HM, int ME, int NS, bool HR, int PM>
 struct FixedSmem {
-  FixedStage<TC, HM, ME, HR> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
-  FixedScratch<TC, HM, ME, HR, FUSEP> sc;
-  uint64_t full_bar[NS], empty_bar[NS];
+  FixedStage<TC, HM, ME, HR, PM == 2> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
+  FixedScratch<TC, HM, ME, HR, PM != 0> sc;
+  uint64_t full_bar[NS], empty_bar[NS], prim_bar[NS];
   uint64_t flux_bar; /* FUSEP: every consumer thread arrives when its edges of the tile are done (split barrier, see phase 3) */
   double wval[16];
   int wargs[16];
@@ -117,10 +128,11 @@ __device__ __noinline__ void fixed_neighbour_wait(const unsigned int *flags, int
   __threadfence_system();
 }
 
-template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT, bool FUSEP>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT, int PM>
 __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const FixedArgs q) {
   extern __shared__ __align__(128) char smem_raw[];
-  using Smem = FixedSmem<TC, HM, ME, NS, HR, FUSEP>;
+  using Smem = FixedSmem<TC, HM, ME, NS, HR, PM>;
+  constexpr bool FUSEP = PM == 1, PRODP = PM == 2, SPLITB = PM != 0;
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const TiledArgs &p = q.t;
   const SweArgs &a = p.a;
@@ -128,7 +140,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
   constexpr int HK = (HM + 31) / 32; /* halo indices per producer lane */
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) {
-      mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], NCONS);
+      mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], NCONS); mbar_init(&S.prim_bar[s], 32);
       /* the zero flux entry that empty cell-edge slots point at (never touched by the bulk copies: nedge <= ME - 2) */
       S.st[s].esn[ME - 1] = 0.0; S.st[s].ecn[ME - 1] = 0.0; S.st[s].elen[ME - 1] = 0.0;
       if (HR) { S.st[s].f1r[ME - 1] = 0.0; S.st[s].f2r[ME - 1] = 0.0; }
@@ -217,6 +229,26 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
         }
       }
       cp_async_arrive_noinc(bar);
+      if (PRODP) {
+        /* the consumers are busy with the previous tile and the next stage is not free yet: this warp has nothing else to do.  Wait
+         * for the copies just issued, derive u, v, sqrt(h) of every staged cell (two cells per lane and sweep: two independent
+         * dependency chains) and announce them; the consumers wait on prim_bar instead of full_bar. */
+        mbar_wait(bar, (it / NS) & 1);
+        const double tiny_p = a.tiny_h, ha2_p = a.ha2;
+        const int nst = TC + nhalo;
+        for (int x = lane; x < nst; x += 64) {
+          const int y = x + 32;
+          const bool two = y < nst;
+          const double h0 = st.h[x], h1 = two ? st.h[y] : 1.0;
+          double u0, w0, u1, w1;
+          swe_velocities<HR>(h0, st.hu[x], st.hv[x], tiny_p, ha2_p, u0, w0);
+          swe_velocities<HR>(h1, two ? st.hu[y] : 0.0, two ? st.hv[y] : 0.0, tiny_p, ha2_p, u1, w1);
+          st.u[x] = u0; st.v[x] = w0;
+          if (!HR) st.sq[x] = swe_sqrt(h0);
+          if (two) { st.u[y] = u1; st.v[y] = w1; if (!HR) st.sq[y] = swe_sqrt(h1); }
+        }
+        mbar_arrive(&S.prim_bar[s]);
+      }
       d0 = n0; d1 = n1; n0 = nn0; n1 = nn1;
 #pragma unroll
       for (int k = 0; k < HK; ++k) hidx[k] = nh[k];
@@ -234,6 +266,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
   int it = 0;
   for (int tile = q.tile_begin + blockIdx.x; tile < q.tile_end; tile += G, ++it) {
     const int s = it % NS;
+    if (PRODP) mbar_wait(&S.prim_bar[s], (it / NS) & 1); /* the producer has seen the stage land and has added the primitive state */
     mbar_wait(&S.full_bar[s], (it / NS) & 1);
     auto &st = S.st[s];
     const int cb = st.desc[0], ncell = st.desc[1], eo = st.desc[2], nedge = st.desc[3], nhalo = st.desc[5];
@@ -246,7 +279,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
     /* ---- phase 1: primitive state of the staged cells: tile cells [0,TC) and halo cells [TC,TC+nhalo) ----
      * (FUSEP: folded into phase 2 - each edge derives u, v, sqrt(h) of its two sides from one MUFU seed per side, which costs
      * fewer instructions than this pass + its loads, and removes a pass, a CTA barrier and 7 KB of scratch per CTA) */
-    if (!FUSEP) {
+    if (PM == 0) {
       for (int x = tid; x < TC + nhalo; x += NCONS) {
         const double h = st.h[x];
         double u, w;
@@ -264,7 +297,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
       const double sn = st.esn[e], cn = st.ecn[e], len = st.elen[e];
       double hl = st.h[l];
       RoeFlux f = {0.0, 0.0, 0.0, 0.0};
-      double k1l = 0.0, k2l = 0.0, k1r = 0.0, k2r = 0.0;
+      double dl = 0.0, dr = 0.0; /* HR: h^2 - h*^2 of the two sides (the pressure corrections are formed after the Roe flux: 2 live values instead of 4) */
       if (r != 0xffff) {
         double hr = st.h[r];
         if (!(hl < tiny && hr < tiny)) {
@@ -272,6 +305,9 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
           if (FUSEP) {
             if (HR) { swe_velocities<true>(hl, st.hu[l], st.hv[l], tiny, ha2, ul, vl); swe_velocities<true>(hr, st.hu[r], st.hv[r], tiny, ha2, ur, vr); }
             else { swe_edge_side(hl, st.hu[l], st.hv[l], tiny, ha2, ul, vl, sql); swe_edge_side(hr, st.hu[r], st.hv[r], tiny, ha2, ur, vr, sqr); }
+          } else if (PRODP) {
+            ul = st.u[l]; vl = st.v[l]; ur = st.u[r]; vr = st.v[r];
+            if (!HR) { sql = st.sq[l]; sqr = st.sq[r]; }
           } else {
             ul = sc.u[l]; vl = sc.v[l]; ur = sc.u[r]; vr = sc.v[r];
           }
@@ -279,12 +315,11 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
           if (HR) {
             const double zl = st.z[l], zr = st.z[r], zmax = fmax(zl, zr);
             const double hls = fmax(0.0, (hl + zl) - zmax), hrs = fmax(0.0, (hr + zr) - zmax);
-            const double corl = 0.5 * g * (hl * hl - hls * hls) * len, corr = 0.5 * g * (hr * hr - hrs * hrs) * len;
-            k1l = corl * cn; k2l = corl * sn; k1r = corr * cn; k2r = corr * sn;
+            dl = hl * hl - hls * hls; dr = hr * hr - hrs * hrs;
             hl = hls; hr = hrs;
             do_flux = (hls > tiny || hrs > tiny);
             sql = swe_sqrt(hl); sqr = swe_sqrt(hr);
-          } else if (!FUSEP) {
+          } else if (PM == 0) {
             sql = sc.sq[l]; sqr = sc.sq[r];
           }
           if (do_flux) {
@@ -325,8 +360,13 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
         }
       }
       const double fl1 = f.f1 * len, fl2 = f.f2 * len;
-      st.esn[e] = f.f0 * len; st.ecn[e] = fl1 + k1l; st.elen[e] = fl2 + k2l; /* in place of the edge geometry */
-      if (HR) { st.f1r[e] = fl1 + k1r; st.f2r[e] = fl2 + k2r; }
+      if (HR) {
+        const double corl = 0.5 * g * dl * len, corr = 0.5 * g * dr * len;
+        st.esn[e] = f.f0 * len; st.ecn[e] = fl1 + corl * cn; st.elen[e] = fl2 + corl * sn; /* in place of the edge geometry */
+        st.f1r[e] = fl1 + corr * cn; st.f2r[e] = fl2 + corr * sn;
+      } else {
+        st.esn[e] = f.f0 * len; st.ecn[e] = fl1; st.elen[e] = fl2; /* in place of the edge geometry */
+      }
     }
     /* ---- phase 3: per-cell flux sum (branch-free), sources, update ----
      * FUSEP: the barrier between the edge pass and the cell pass is SPLIT (an mbarrier: arrive now, wait later).  Between the two a
@@ -335,7 +375,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
      * instead of two used to idle at the barrier; now they overlap it with this work, and only the flux sum and the update remain
      * behind the wait. */
     static_assert(TC <= NCONS, "one cell per consumer thread");
-    if (FUSEP) {
+    if (SPLITB) {
       mbar_arrive(&S.flux_bar);
       const int t = tid;
       const bool has = t < ncell;
@@ -468,37 +508,49 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
 }
 
 /* ---------------- host side ---------------- */
-template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT, bool FUSEP>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC, bool EULER, bool COURANT, int PM>
 static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
   static PersistentCache cache = {};
-  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, NS, MINB, HR, SRC, EULER, COURANT, FUSEP>;
-  const size_t smem = sizeof(FixedSmem<TC, HM, ME, NS, HR, FUSEP>);
+  auto kern = swe_tiled_fixed_kernel<TC, HM, ME, NCONS, NS, MINB, HR, SRC, EULER, COURANT, PM>;
+  const size_t smem = sizeof(FixedSmem<TC, HM, ME, NS, HR, PM>);
   int grid = 0;
   RDYB_CALL(persistent_grid(kern, NCONS + 32, smem, ntiles, cache, "fixed tile kernel", &grid));
   kern<<<grid, NCONS + 32, smem, stream>>>(q);
   return RDYB_SUCCESS;
 }
 
-/* FUSEP (the default) folds the primitive-state pass into the edge pass; RDYB_K4_PRIM_PASS=1 restores the three-pass kernel (A/B) */
-static inline bool fixed_prim_pass() {
-  static int v = -1;
-  if (v < 0) { const char *e = getenv("RDYB_K4_PRIM_PASS"); v = (e && e[0] == '1') ? 1 : 0; }
-  return v == 1;
+/* which variant computes the primitive state (see FixedSmem): RDYB_K4_PRIM = 0 | 1 | 2 (A/B runs); RDYB_K4_PRIM_PASS=1 is the old
+ * spelling of 0.  Default: 2 (producer warp) for the Roe kernel, 1 (per edge side) for HR, whose larger stage leaves no room for the
+ * per-stage primitive arrays at three CTAs per SM. */
+static inline int fixed_prim_mode(bool hr) {
+  static int v = -2;
+  if (v == -2) {
+    const char *e = getenv("RDYB_K4_PRIM"), *o = getenv("RDYB_K4_PRIM_PASS");
+    v = -1;
+    if (e && e[0] >= '0' && e[0] <= '2') v = e[0] - '0';
+    else if (o && o[0] == '1') v = 0;
+  }
+  if (v >= 0) return (hr && v == 2) ? 1 : v;
+  return hr ? 1 : RDYB_K4_DEFAULT_PRIM;
 }
-template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, bool FUSEP>
+template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int PM>
 static int fixed_launch_cfg2(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
 #define FL(SRCv)                                                                                                                   \
-  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, true, FUSEP>(q, nt, stream)                           \
-                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, false, FUSEP>(q, nt, stream))                         \
-         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, true, FUSEP>(q, nt, stream)                          \
-                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, false, FUSEP>(q, nt, stream)))
+  (euler ? (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, true, PM>(q, nt, stream)                              \
+                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, true, false, PM>(q, nt, stream))                            \
+         : (courant ? fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, true, PM>(q, nt, stream)                             \
+                    : fixed_launch_t<TC, HM, ME, NCONS, NS, MINB, HR, SRCv, false, false, PM>(q, nt, stream)))
   return xq ? FL(1) : FL(0);
 #undef FL
 }
 template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR>
 static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
-  return fixed_prim_pass() ? fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, false>(q, nt, xq, euler, courant, stream)
-                           : fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, true>(q, nt, xq, euler, courant, stream);
+  const int pm = fixed_prim_mode(HR);
+  if (pm == 0) return fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 0>(q, nt, xq, euler, courant, stream);
+  if constexpr (!HR) {
+    if (pm == 2) return fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 2>(q, nt, xq, euler, courant, stream);
+  }
+  return fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 1>(q, nt, xq, euler, courant, stream);
 }
 
 /* the compiled tile shapes: {tile cells, halo capacity, edge capacity (the last entry is the zero flux), consumer threads,
