@@ -519,7 +519,7 @@ def run_b200_arm(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (traffic * n_owned if traffic else None), "traffic_note": traffic_note, "peak_source": peak_src,
                          "algorithmic_bytes_per_cell": bytes_per_cell, "algorithmic_bytes_per_cell_per_step": bytes_per_step_cell,
-                         "kernel": ("muscl_gradient_kernel + " + ("swe_gather_kernel<RECON>" if kernel == GATHER else "swe_tiled_muscl_kernel")) if args.second_order else "swe_%s_kernel" % kernel_name,
+                         "kernel": ("muscl_gradient_kernel + " + ("swe_gather_kernel<RECON>" if kernel == GATHER else "swe_tiled_muscl_async_kernel (K3M)")) if args.second_order else "swe_%s_kernel" % kernel_name,
                          "note": "per-GPU: algorithmic bytes of one step on rank 0 / CUDA-event time per step on the launching stream (max over ranks)"},
             "e2e": e2e,
             "gpu_launches": int(launches),

@@ -667,7 +667,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile */
     op->courant_arg_tiled = true;
-    if (getenv("RDYB_MUSCL_ASYNC") && tiled_muscl_async_applicable(op->T, op->t_edge_off)) { /* opt-in until it has run on a B200 (swe_tiled_muscl_async.cuh) */
+    if (!getenv("RDYB_MUSCL_K2M") && tiled_muscl_async_applicable(op->T, op->t_edge_off)) { /* K3M: 15 % faster than K2M on the B200 (profiles/r2_bench_so_*.json); RDYB_MUSCL_K2M=1 keeps K2M */
       op->last_kernel = "swe_tiled_muscl_async_kernel (K3M, MUSCL) + muscl_gradient_kernel";
       RDYB_CALL(tiled_muscl_async_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));
     } else {

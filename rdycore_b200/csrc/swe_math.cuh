@@ -51,6 +51,14 @@ __device__ __forceinline__ double swe_sqrt(double a) {
   return a >= RDYB_TINY_ARG ? s : 0.0;
 }
 
+/* sqrt(a) = a * rsqrt(a) without the Heron correction: <= ~1.5 ulp instead of <= ~1 ulp, three fp64 instructions fewer.  Used per
+ * edge side in K4's edge pass, where sqrt(h) only enters the Roe averages and the celerities (an error of one ulp there is the
+ * effect of a 2-ulp change of h). */
+__device__ __forceinline__ double swe_sqrt_fast(double a) {
+  const double y = swe_rsqrt_core(a >= RDYB_TINY_ARG ? a : 1.0);
+  return a >= RDYB_TINY_ARG ? a * y : 0.0;
+}
+
 /* a^(-1/3) for normal positive a (depths in [tiny_h, ~1e4]): fp32 MUFU seed exp2(-log2(a)/3) (~2^-21) + two Newton steps
  * y <- y + y (1 - a y^3) / 3 (error e -> 2 e^2), ~15 instructions instead of the ~40 of the library rcbrt() with its
  * exponent-splitting and special-case paths */
@@ -85,24 +93,17 @@ __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, d
 
 /* Primitive state of one edge side, computed where the edge needs it (K4's fused variant: no per-cell pass, no u/v/sqrt(h)
  * scratch, one CTA barrier per tile less): u, v as swe_velocities<false> and sq = sqrt(h), from ONE MUFU seed.  With
- * y = 1/sqrt(h): sqrt(h) = h y (+ a Heron correction), 1/h = y y (+ one Newton correction), both <= ~1 ulp.  The general
+ * y = 1/sqrt(h) (two Newton steps, ~1 ulp): sqrt(h) = h y and 1/h = y y, ~1.5 and ~2.5 ulp - no correction steps: the parity
+ * tests bound the effect (it is far below the difference between pow(x, .5) on the CPU and any sqrt here).  The general
  * regularised form hu h / (h^2 + h_a^2) is kept for h_a != 0 (a uniform branch). */
 __device__ __forceinline__ void swe_edge_side(double h, double hu, double hv, double tiny_h, double ha2, double &u, double &v, double &sq) {
   const bool pos = h >= RDYB_TINY_ARG;
   const double hs = pos ? h : 1.0;
   const double y = swe_rsqrt_core(hs);
-  double s = hs * y;
-  const double r = fma(-s, s, hs);
-  s = fma(r, 0.5 * y, s);
-  sq = pos ? s : 0.0;
+  sq = pos ? hs * y : 0.0;
   double inv;
-  if (ha2 == 0.0) {
-    inv = y * y;
-    const double e = fma(-hs, inv, 1.0);
-    inv = fma(inv, e, inv);
-  } else {
-    inv = hs * swe_rcp(hs * hs + ha2);
-  }
+  if (ha2 == 0.0) inv = y * y; /* 1/h to ~2.5 ulp */
+  else inv = hs * swe_rcp(hs * hs + ha2);
   const bool wet = !(h < tiny_h);
   u = wet ? hu * inv : 0.0;
   v = wet ? hv * inv : 0.0;
@@ -121,8 +122,10 @@ __device__ __forceinline__ RoeFlux swe_roe_flux_t(double hl, double ul, double v
   const double cl = RDYB_SQRT_GRAVITY * sql, cr = RDYB_SQRT_GRAVITY * sqr; /* sqrt(g*h) */
   const double hhat = duml * dumr;
   const double rsum = swe_rcp(duml + dumr);
-  const double uhat = (duml * ul + dumr * ur) * rsum;
-  const double vhat = (duml * vl + dumr * vr) * rsum;
+  /* (duml ul + dumr ur) / (duml + dumr) = ul + w (ur - ul) with w = dumr / (duml + dumr): one FMA per component */
+  const double wr = dumr * rsum;
+  const double uhat = fma(wr, ur - ul, ul);
+  const double vhat = fma(wr, vr - vl, vl);
   const double c2 = 0.5 * g * (hl + hr);
   const double rchat = swe_rsqrt_core(c2); /* c2 >= g tiny_h / 2: normal */
   const double chat = c2 * rchat;

@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
             dl = hl * hl - hls * hls; dr = hr * hr - hrs * hrs;
             hl = hls; hr = hrs;
             do_flux = (hls > tiny || hrs > tiny);
-            sql = swe_sqrt(hl); sqr = swe_sqrt(hr);
+            sql = swe_sqrt_fast(hl); sqr = swe_sqrt_fast(hr);
           } else if (PM == 0) {
             sql = sc.sq[l]; sqr = sc.sq[r];
           }

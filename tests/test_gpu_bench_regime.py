@@ -77,7 +77,7 @@ def test_k2m_second_order_one_million_cells_against_the_oracle():
     op.set_kernel(TILED, 128)
     op.step_euler(case.dt, STEPS)
     u = op.get_state()
-    assert "K2M" in op.kernel_info()
+    assert "K3M" in op.kernel_info() or "K2M" in op.kernel_info()
     assert_state_close(u, u_ref, what="1 M cells second order")
     op.close()
 

@@ -13,6 +13,11 @@ from rdycore_b200.operator import GATHER, TILED, TILED_FIXED, Operator
 from util import assert_state_close, make_oracle
 
 pytestmark = pytest.mark.gpu
+
+
+def _tiled_muscl(info: str) -> bool:
+    """the second-order path ran on the tiled layout: K3M (bulk-async staged, the default) or K2M (RDYB_MUSCL_K2M=1 / shapes K3M cannot stage)"""
+    return "K3M" in info or "K2M" in info
 LIMITERS = [cases.MUSCL_MINMOD, cases.MUSCL_NONE, cases.MUSCL_VANLEER]
 
 
@@ -39,7 +44,7 @@ def test_dam_break_quads_second_order(reconstruction, source_method):
     steps = 150 if reconstruction == cases.MUSCL_VANLEER else 400
     op.step_euler(case.dt, steps)
     oracle.step_euler(case.dt, steps)
-    assert "K2M, MUSCL" in op.kernel_info()
+    assert _tiled_muscl(op.kernel_info()) and "MUSCL)" in op.kernel_info()
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order dam break")
     first = cases.dam_break_quads(nx=60, ny=60, source_method=source_method)
     o1 = make_oracle(first)
@@ -78,7 +83,7 @@ def test_second_order_rhs_courant_and_rk4(kernel):
     fd = oracle.array("flux_divergence").reshape(-1, 3)
     assert (np.abs(op.get_field(0) - fd) / np.abs(fd).max(axis=0)).max() < 1e-12
     assert op.courant().max_courant_num == pytest.approx(oracle.courant(), rel=1e-12)
-    assert ("K2M" in op.kernel_info()) == (kernel == TILED)
+    assert _tiled_muscl(op.kernel_info()) == (kernel == TILED)
     d = op.courant()  # the arg of the maximum names an internal edge and one of its two cells, whichever kernel reported it
     ecells = case.mesh.view_arrays()["edge_cell_ids"].reshape(-1, 2)
     assert d.global_cell_id in ecells[d.global_edge_id] and ecells[d.global_edge_id].min() >= 0
@@ -112,7 +117,7 @@ def test_tiled_and_gather_second_order_agree(reconstruction, monkeypatch):
     u_local = oracle.array("u_local")
     assert np.abs(u_local.reshape(-1, 3)[:, 1:]).max() > 0.0
     F = [op.apply_host(case.dt, u_local) for op in ops]
-    assert "K2M" in ops[0].kernel_info() and "K1, MUSCL" in ops[1].kernel_info() and "K1, MUSCL" in ops[2].kernel_info()
+    assert _tiled_muscl(ops[0].kernel_info()) and "K1, MUSCL" in ops[1].kernel_info() and "K1, MUSCL" in ops[2].kernel_info()
     scale = np.abs(F[1]).max(axis=0)
     assert (np.abs(F[0] - F[1]) / scale).max() < 1e-14
     assert np.array_equal(F[1], F[2])
@@ -130,9 +135,6 @@ def test_hr_with_second_order_is_refused_like_the_reference():
         make_oracle(case)
 
 
-@pytest.mark.skipif(not os.environ.get("RDYB_TEST_UNVERIFIED"),
-                    reason="K3M (swe_tiled_muscl_async.cuh) was written after round 1's GPU time was spent: it is opt-in and its tests "
-                           "run only with RDYB_TEST_UNVERIFIED=1 (under a timeout: an mbarrier byte-count error would hang) until it is green")
 @pytest.mark.parametrize("reconstruction", LIMITERS)
 @pytest.mark.parametrize("tile", [128, 224])
 def test_async_tiled_second_order(reconstruction, tile, monkeypatch):
@@ -142,11 +144,12 @@ def test_async_tiled_second_order(reconstruction, tile, monkeypatch):
     oracle = make_oracle(case)
     oracle.rhs(case.dt)
     u_local = oracle.array("u_local").copy()
+    monkeypatch.setenv("RDYB_MUSCL_K2M", "1")
     ref = Operator.from_case(case)
     ref.set_kernel(TILED, tile)
     ref.set_options(courant=True)
     F_ref = ref.apply_host(case.dt, u_local)
-    monkeypatch.setenv("RDYB_MUSCL_ASYNC", "1")
+    monkeypatch.delenv("RDYB_MUSCL_K2M")
     op = Operator.from_case(case)
     op.set_kernel(TILED, tile)
     op.set_options(courant=True)
@@ -154,7 +157,8 @@ def test_async_tiled_second_order(reconstruction, tile, monkeypatch):
     assert "K3M" in op.kernel_info() and "K2M" in ref.kernel_info()
     assert (np.abs(F - F_ref) / np.abs(F_ref).max(axis=0)).max() < 1e-14  # the same expressions, compiled in two kernels
     assert op.courant().max_courant_num == pytest.approx(ref.courant().max_courant_num, rel=1e-14)
-    steps = 100
+    # unlimited extrapolation + forward Euler is unstable in the reference scheme itself (the oracle reaches NaN by step 100)
+    steps = 30 if reconstruction == cases.MUSCL_NONE else 100
     if reconstruction == cases.MUSCL_VANLEER:
         op.step_rk4(case.dt, steps); oracle.step_rk4(case.dt, steps)
     else:

@@ -96,12 +96,9 @@ def test_two_ranks_second_order_exchanges_gradients():
     _run(2, ["--recon", "1", "--kernel", "0", "--steps", "60"], 29561)
 
 
-@pytest.mark.skipif(not os.environ.get("RDYB_TEST_UNVERIFIED"),
-                    reason="the tiled second-order kernel (K2M) is parity-green on one GPU; its 2-GPU run had to wait for round 2's GPU "
-                           "minutes (DESIGN.md section 8) - run with RDYB_TEST_UNVERIFIED=1")
 def test_two_ranks_second_order_on_the_tiled_layout():
     """K2M on a partitioned mesh: frontier tiles list ghost cells in their halo and read the exchanged ghost gradients."""
     if _ngpus() < 2:
         pytest.skip("needs 2 GPUs")
     out = _run(2, ["--recon", "1", "--kernel", "1", "--tile", "128", "--steps", "60"], 29571)
-    assert "K2M" in out
+    assert "K3M" in out or "K2M" in out
