@@ -118,6 +118,16 @@ typedef struct {
   const int32_t *recv_cells;   /* local ids of ghost cells, per peer, ascending global id */
 } RdybHaloView;
 
+/* Vertex data for Bradford-Sanders well balancing (rdyb_operator_enable_bs2002): RDyVertices.points[].X[2],
+ * RDyCells.vertex_offsets / vertex_ids, RDyEdges.vertex_ids (include/private/rdymeshimpl.h:40-44,96,117), view-local numbering */
+typedef struct {
+  int32_t        num_vertices;
+  const double  *vertex_z;            /* [num_vertices] */
+  const int32_t *cell_vertex_offsets; /* [num_cells+1] */
+  const int32_t *cell_vertex_ids;
+  const int32_t *edge_vertex_ids;     /* [2*num_edges]: beginning and end vertex of every edge */
+} RdybVertexView;
+
 typedef struct RdybOperator_ *RdybOperator;
 
 const char *rdyb_last_error(void);
@@ -192,6 +202,13 @@ int rdyb_operator_step_euler(RdybOperator op, double dt, int32_t nsteps);
 /* classical RK4 (TSRK4) built from the RHS-only kernel and AXPY stage kernels */
 int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps);
 int rdyb_operator_synchronize(RdybOperator op);
+
+/* ---- Bradford-Sanders (2002) well balancing with the semantics of the reference's libCEED operator (the PETSc operator ignores the
+ * option, src/operator.c:202-209, and so does rdyb_operator_create): a vertex pass (SWEEtaVertex, src/swe/swe_well_balancing.h:30)
+ * before every RHS evaluation and g dhv^2 / 24 (cn, sn) on every edge flux (src/swe/swe_fluxes_ceed.h:15-19,
+ * src/swe/swe_roe_flux_ceed.h:119-121).  Triangles, serial meshes, first order; runs on the cell-centric kernel K1. */
+int rdyb_operator_enable_bs2002(RdybOperator op, const RdybVertexView *vertices);
+int rdyb_operator_get_eta_vertices(RdybOperator op, int32_t num_vertices, double *eta);
 
 /* ---- one coupling interval on the device: RDyAdvance without a host round trip (src/rdyadvance.c:261-383) ----
  * rdyb_operator_time_set puts (t, dt) into a device-resident control block.  rdyb_operator_advance_device then enqueues ONE CUDA

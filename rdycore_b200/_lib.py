@@ -67,6 +67,11 @@ class RdybCourantDiagnostics(C.Structure):
     _fields_ = [("max_courant_num", C.c_double), ("global_edge_id", C.c_int64), ("global_cell_id", C.c_int64)]
 
 
+class RdybVertexView(C.Structure):
+    _fields_ = [("num_vertices", C.c_int32), ("vertex_z", C.POINTER(C.c_double)), ("cell_vertex_offsets", c_i32p), ("cell_vertex_ids", c_i32p),
+                ("edge_vertex_ids", c_i32p)]
+
+
 class RdybHaloView(C.Structure):
     _fields_ = [
         ("num_peers", C.c_int32),
@@ -97,7 +102,7 @@ OPERATOR_SYMBOLS = [
     "rdyb_operator_device_pointer", "rdyb_operator_last_kernel_ms", "rdyb_operator_set_kernel", "rdyb_operator_get_field",
     "rdyb_host_alloc", "rdyb_host_free", "rdyb_operator_kernel_info", "rdyb_operator_halo_export", "rdyb_operator_halo_import",
     "rdyb_operator_set_external_source_aos", "rdyb_operator_get_courant_global", "rdyb_operator_set_max_ctas",
-    "rdyb_operator_get_wait_cycles", "rdyb_operator_time_set", "rdyb_operator_time_get", "rdyb_operator_advance_device", "rdyb_host_sync_count",
+    "rdyb_operator_get_wait_cycles", "rdyb_operator_time_set", "rdyb_operator_time_get", "rdyb_operator_advance_device", "rdyb_host_sync_count", "rdyb_operator_enable_bs2002", "rdyb_operator_get_eta_vertices",
 ]
 
 _lib = None

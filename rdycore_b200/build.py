@@ -95,7 +95,7 @@ def build_oracles() -> None:
     """Build the CPU oracles (test infrastructure): the port always, oracle/_ref where the reference tree exists."""
     # `adapter`: rdycore_adapter.c (factories with the reference's signatures) against the reference's headers + librdyb200.so - the
     # object under test of tests/test_gpu_rdycore_adapter.py, built where the reference tree exists, after the library
-    p = subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port", "ref", "adapter"], capture_output=True, text=True)
+    p = subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port", "ref", "adapter", "bs2002"], capture_output=True, text=True)
     if p.returncode != 0:
         sys.stderr.write(p.stdout + p.stderr)
         raise RuntimeError("building the CPU oracles failed")

@@ -135,6 +135,13 @@ struct RdybOperator_ {
     int adaptive = -1, kernel_kind = -1, tile_cells = -1, opts = -1, max_ctas = -1;
     const double *src_sig = nullptr;
   } adv;
+  /* Bradford-Sanders well balancing (libCEED semantics, rdyb_operator_enable_bs2002) */
+  struct {
+    bool enabled = false;
+    int32_t nv = 0;
+    double *vz = nullptr, *eta = nullptr, *cz = nullptr; /* vertex z, vertex eta, sorted vertex z per device cell [3][stride] */
+    int32_t *vc_off = nullptr, *vc_cell = nullptr, *vb = nullptr, *ve = nullptr;
+  } bs;
   const AdvCtl *adv_ctl_arg = nullptr; /* set around the launches captured into the device-side loop: fill_args passes it on */
   int adv_buf_arg = 0;
   int max_ctas = 0; /* cap on the grid of the persistent kernels (0 = none): rdyb_operator_set_max_ctas */
@@ -217,6 +224,8 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   if (op->stream) rdyb_stream_sync(op->stream);
   if (op->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(op->comm);
   for (int i = 0; i < op->p2p_nopened; ++i) cudaIpcCloseMemHandle(op->p2p_opened[i]);
+  for (void *q : {(void *)op->bs.vz, (void *)op->bs.eta, (void *)op->bs.cz, (void *)op->bs.vc_off, (void *)op->bs.vc_cell, (void *)op->bs.vb, (void *)op->bs.ve})
+    if (q) cudaFree(q);
   adv_release_graph(op);
   if (op->adv.ctl) cudaFree(op->adv.ctl);
   if (op->adv.mirror) cudaFreeHost(op->adv.mirror);
@@ -626,6 +635,7 @@ static void fill_args(RdybOperator op, SweArgs &a, const double *in, double *out
   a.stride = op->stride; a.width = op->width; a.begin = 0; a.end = 0;
   a.grad = op->grad; a.gcx = op->m_gcx; a.gcy = op->m_gcy; a.dxs = op->m_dxs; a.dys = op->m_dys; a.dxn = op->m_dxn; a.dyn = op->m_dyn;
   a.ctl = op->adv_ctl_arg; a.ctl_buf = op->adv_buf_arg;
+  if (op->bs.enabled) { a.bs_eta = op->bs.eta; a.bs_vz = op->bs.vz; a.bs_vb = op->bs.vb; a.bs_ve = op->bs.ve; }
   a.dt = dt; a.tiny_h = op->cfg.tiny_h; a.ha2 = op->cfg.h_anuga_regular * op->cfg.h_anuga_regular; a.xq_thr = op->cfg.xq2018_threshold;
 }
 
@@ -678,7 +688,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     CU(cudaGetLastError());
     return RDYB_SUCCESS;
   }
-  if (op->kernel_kind >= 1 && op->has_tiled && !op->recon) { /* first order: the tiled kernels */
+  if (op->kernel_kind >= 1 && op->has_tiled && !op->recon && !op->bs.enabled) { /* first order: the tiled kernels (the BS2002 term lives in K1 only) */
     op->courant_arg_tiled = true;
     /* interior tiles and frontier tiles (thin strips along the partition border, with many more outside neighbours) are
      * launched separately so that each part can use the most specialised kernel its tiles fit */
@@ -940,6 +950,12 @@ static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool eu
   /* a partitioned mesh whose ghosts nobody fills would silently compute on stale values */
   RDYB_CHECK(op->L.num_peers == 0 || op->comm || op->ghosts_from_caller, RDYB_ERR_USER,
              "this rank has %d neighbour ranks but no communicator: call rdyb_operator_init_comm (or use rdyb_operator_apply_host, whose u_local carries the ghosts)", op->L.num_peers);
+  if (op->bs.enabled) { /* CreateCeedEtaVerticesOperator runs before the flux operator in every RHS evaluation (src/operator.c:170-192) */
+    bs2002_eta_vertex_kernel<<<grid_for(op->bs.nv, 128), 128, 0, op->stream>>>(in, op->bs.cz, op->stride, op->bs.vc_off, op->bs.vc_cell, op->bs.nv, op->cfg.tiny_h,
+                                                                           op->bs.eta);
+    LAUNCHED();
+    CU(cudaGetLastError());
+  }
   if (op->recon) {
     /* second order: state halo, gradients of the owned cells, gradient halo (two [3][stride] blocks: d/dx and d/dy, the two
      * passes of CommunicateCellGradients), then the reconstructed fluxes.  No overlap yet: this row is correctness-first. */
@@ -1194,6 +1210,75 @@ extern "C" int rdyb_operator_get_wait_cycles(RdybOperator op, uint64_t *sum, uin
   return RDYB_SUCCESS;
 }
 
+
+/* ---------------- Bradford-Sanders (2002) well balancing, libCEED semantics ----------------
+ * `physics.flow.well_balancing: bradford_sanders_2002` changes the reference's libCEED operator only (src/operator.c:170-192): a
+ * vertex pass computes the water-surface elevation at every mesh vertex from the cells around it (SWEEtaVertex), and every edge flux
+ * gains g dhv^2 / 24 (cn, sn), dhv = the change of the vertex depth along the edge (ComputeDhv).  The PETSc operator this library
+ * replaces ignores the option (src/operator.c:202-209), and so does rdyb_operator_create: BS2002 is switched on by THIS call, which
+ * hands over the vertex data the mesh view does not carry.  Triangles, serial meshes, first order, K1. */
+extern "C" int rdyb_operator_enable_bs2002(RdybOperator op, const RdybVertexView *vv) {
+  RDYB_CHECK(op && vv && vv->vertex_z && vv->cell_vertex_offsets && vv->cell_vertex_ids && vv->edge_vertex_ids, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(op->L.num_peers == 0, RDYB_ERR_SUP, "BS2002 well balancing is implemented for serial meshes");
+  RDYB_CHECK(!op->recon && op->cfg.well_balancing != RDYB_WELL_BALANCING_HR, RDYB_ERR_USER, "BS2002 well balancing goes with the first-order Roe flux");
+  CU(cudaSetDevice(op->device));
+  const RdybLayout &L = op->L;
+  const int32_t nv = vv->num_vertices, nc = op->NL;
+  RDYB_CHECK(nv > 0, RDYB_ERR_ARG, "no vertices");
+  std::vector<double> cz(3 * (size_t)op->stride, 0.0);
+  std::vector<int32_t> off((size_t)nv + 1, 0);
+  for (int32_t c = 0; c < nc; ++c) { /* c = view-local cell id */
+    const int32_t o = vv->cell_vertex_offsets[c], n = vv->cell_vertex_offsets[c + 1] - o;
+    RDYB_CHECK(n == 3, RDYB_ERR_SUP, "BS2002 well balancing is defined on triangles (cell %d has %d vertices), src/swe/swe_well_balancing.h:30", c, n);
+    double z[3];
+    for (int k = 0; k < 3; ++k) {
+      const int32_t v = vv->cell_vertex_ids[o + k];
+      RDYB_CHECK(v >= 0 && v < nv, RDYB_ERR_ARG, "vertex id %d out of range", v);
+      z[k] = vv->vertex_z[v];
+      off[(size_t)v + 1]++;
+    }
+    std::sort(z, z + 3);
+    const int32_t d = L.local_to_dev[c];
+    for (int k = 0; k < 3; ++k) cz[(size_t)k * op->stride + d] = z[k];
+  }
+  for (int32_t v = 0; v < nv; ++v) off[(size_t)v + 1] += off[v];
+  std::vector<int32_t> cells((size_t)off[nv]), fill(off.begin(), off.end() - 1);
+  for (int32_t c = 0; c < nc; ++c) /* ascending view-local cell id per vertex: the summation order of the oracle */
+    for (int k = 0; k < 3; ++k) cells[(size_t)fill[vv->cell_vertex_ids[vv->cell_vertex_offsets[c] + k]]++] = L.local_to_dev[c];
+  const size_t W = (size_t)L.width * (size_t)L.stride;
+  std::vector<int32_t> vb(W, 0), ve(W, 0);
+  for (size_t q = 0; q < W; ++q) {
+    const int32_t e = L.ell_edge[q];
+    if (e >= 0) { vb[q] = vv->edge_vertex_ids[2 * (size_t)e]; ve[q] = vv->edge_vertex_ids[2 * (size_t)e + 1]; }
+  }
+  auto &B = op->bs;
+  for (void *q : {(void *)B.vz, (void *)B.eta, (void *)B.cz, (void *)B.vc_off, (void *)B.vc_cell, (void *)B.vb, (void *)B.ve})
+    if (q) cudaFree(q);
+  B = {};
+  RDYB_CALL(upload(&B.vz, vv->vertex_z, (size_t)nv));
+  RDYB_CALL(upload(&B.eta, vv->vertex_z, (size_t)nv)); /* CreateCeedEtaVerticesVector: the vertex elevations until the first pass */
+  RDYB_CALL(upload(&B.cz, cz.data(), cz.size()));
+  RDYB_CALL(upload(&B.vc_off, off.data(), off.size()));
+  RDYB_CALL(upload(&B.vc_cell, cells.data(), cells.size()));
+  RDYB_CALL(upload(&B.vb, vb.data(), W));
+  RDYB_CALL(upload(&B.ve, ve.data(), W));
+  B.nv = nv;
+  B.enabled = true;
+  adv_release_graph(op);
+  return RDYB_SUCCESS;
+}
+
+/* the vertex water-surface elevations of the last right-hand-side evaluation (tests) */
+extern "C" int rdyb_operator_get_eta_vertices(RdybOperator op, int32_t num_vertices, double *eta) {
+  RDYB_CHECK(op && eta, RDYB_ERR_ARG, "NULL argument");
+  RDYB_CHECK(op->bs.enabled, RDYB_ERR_USER, "BS2002 well balancing is not enabled");
+  RDYB_CHECK(num_vertices == op->bs.nv, RDYB_ERR_ARG_SIZ, "Wrong number of vertices: %d (should be %d)", num_vertices, op->bs.nv);
+  CU(cudaSetDevice(op->device));
+  CU(cudaMemcpyAsync(eta, op->bs.eta, sizeof(double) * (size_t)num_vertices, cudaMemcpyDeviceToHost, op->stream));
+  CU(rdyb_stream_sync(op->stream));
+  return RDYB_SUCCESS;
+}
+
 /* ---------------- device-side time loop: one coupling interval without a host round trip ----------------
  * RDyAdvance (src/rdyadvance.c:261-383) = [adaptive-dt rule from the last Courant number, :303-343] + TSSolve to the next
  * coupling time with TS_EXACTFINALTIME_MATCHSTEP + UpdateOperatorDiagnostics (:366-372).  The reference (and round 1 of this
@@ -1295,7 +1380,7 @@ static int adv_resolve(RdybOperator op) {
 }
 
 static bool adv_kernel_supported(RdybOperator op, double dt_probe) {
-  if (op->recon || op->L.num_peers > 0) return false; /* second order / partitioned meshes: host-driven path */
+  if (op->recon || op->L.num_peers > 0 || op->bs.enabled) return false; /* second order / partitioned meshes / BS2002 (a vertex pass per step): host-driven path */
   if (op->kernel_kind == 0) return true;            /* K1 */
   if (op->kernel_kind == 3 && op->has_tiled) {      /* K4, when the mesh fits its compiled shapes and options */
     SweArgs probe;

@@ -59,7 +59,50 @@ struct SweArgs {
    * ctl->cur == ctl_buf (the launch reads state buffer ctl_buf) */
   const AdvCtl *ctl = nullptr;
   int32_t ctl_buf = 0;
+  /* Bradford-Sanders (2002) well balancing, libCEED semantics (K1 only; NULL = off): water-surface elevation at the vertices
+   * (bs2002_eta_vertex_kernel), vertex bed elevations, and per ELL slot the two vertices of the edge (RDyEdges.vertex_ids order) */
+  const double *__restrict__ bs_eta = nullptr, *__restrict__ bs_vz = nullptr;
+  const int32_t *__restrict__ bs_vb = nullptr, *__restrict__ bs_ve = nullptr;
 };
+
+/* ComputeDhv + the well-balancing term of SWERiemannFlux_Roe (src/swe/swe_fluxes_ceed.h:15-19, src/swe/swe_roe_flux_ceed.h:119-121):
+ * g dhv^2 / 24, to be added as (cn, sn) times it to the momentum components of the edge flux */
+__device__ __forceinline__ double swe_bs2002_term(const SweArgs &a, size_t q) {
+  const int vb = a.bs_vb[q], ve = a.bs_ve[q];
+  const double hv_beg = fmax(a.bs_eta[vb] - a.bs_vz[vb], 0.0), hv_end = fmax(a.bs_eta[ve] - a.bs_vz[ve], 0.0);
+  const double dhv = hv_end - hv_beg;
+  return RDYB_GRAVITY * (dhv * dhv) / 24.0;
+}
+
+/* SWEEtaVertex (src/swe/swe_well_balancing.h:30-83) gathered per vertex: eta[v] = sum over the cells around v, in ascending cell id,
+ * of eta_cell(h; z1 <= z2 <= z3) / n_cells(v) (CreateCeedEtaVerticesOperator, src/operator_fluxes_ceed.c:745-859).  One thread per
+ * vertex; no atomics, so the sum has a fixed order. */
+__global__ void bs2002_eta_vertex_kernel(const double *__restrict__ h, const double *__restrict__ cz /* [3][stride] sorted vertex z per cell */, int32_t stride,
+                                         const int32_t *__restrict__ vc_off, const int32_t *__restrict__ vc_cell, int32_t nv, double tiny_h,
+                                         double *__restrict__ eta) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  const int k0 = vc_off[v], k1 = vc_off[v + 1];
+  const double wt = 1.0 / (double)(k1 - k0);
+  double sum = 0.0;
+  for (int k = k0; k < k1; ++k) {
+    const int c = vc_cell[k];
+    const double hc = h[c], z1 = cz[c], z2 = cz[(size_t)stride + c], z3 = cz[2 * (size_t)stride + c];
+    const double h3 = z3 - (z1 + z2 + z3) / 3.0;
+    const double h2 = z2 < z3 ? (z2 - z1) * (z2 - z1) / (3.0 * (z3 - z1)) : h3;
+    double eta_cell = 0.0;
+    if (hc <= tiny_h) eta_cell = z1; /* dry bed */
+    else if (hc >= h3) eta_cell = (z1 + z2 + z3) / 3.0 + hc; /* all vertices submerged */
+    else if (hc > 0.0 && hc <= h2) eta_cell = z1 + cbrt(3.0 * hc * (z2 - z1) * (z3 - z1)); /* one vertex submerged */
+    else if (hc > h2 && hc < h3) { /* two vertices submerged */
+      const double b = z3 - 3.0 * z1;
+      const double c2 = z1 * z2 + z1 * z1 - z3 * z2 - 3.0 * hc * (z3 - z1);
+      eta_cell = 0.5 * (-b + sqrt(b * b - 4.0 * c2));
+    }
+    sum += eta_cell * wt;
+  }
+  eta[v] = sum;
+}
 
 /* slope limiters of the MUSCL reconstruction, src/operator_fluxes_ceed.c:1100-1132: the extrapolated increment is limited
  * against half the cell-to-cell jump */
@@ -200,7 +243,8 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
           double sql, sqr;
           if (HR) { sql = swe_sqrt(hl); sqr = swe_sqrt(hr); }
           else { const double sqn = swe_sqrt(hn); sql = left ? sq : sqn; sqr = left ? sqn : sq; }
-          const RoeFlux f = swe_roe_flux(hl, ul, vl, sql, hr, ur, vr, sqr, sn, cn);
+          RoeFlux f = swe_roe_flux(hl, ul, vl, sql, hr, ur, vr, sqr, sn, cn);
+          if (a.bs_eta) { const double bs = swe_bs2002_term(a, q); f.f1 += bs * cn; f.f2 += bs * sn; }
           if (COURANT) {
             const double cnum = f.amax * fabs(slen) * fmax(ia, a.inv_area[nbr]) * dt_; /* amax*L/min(A_l,A_r)*dt */
             if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }
@@ -229,6 +273,7 @@ __global__ void __launch_bounds__(RDYB_BLOCK) swe_gather_kernel(const SweArgs a)
         RoeFlux f = {0.0, 0.0, 0.0, 0.0};
         if (ok && !(h < tiny && hr < tiny)) {
           f = swe_roe_flux(h, ul, vl, swe_sqrt(h), hr, ur, vr, swe_sqrt(hr), sn, cn);
+          if (a.bs_eta) { const double bs = swe_bs2002_term(a, q); f.f1 += bs * cn; f.f2 += bs * sn; }
           if (COURANT) {
             const double cnum = f.amax * fabs(slen) * ia * dt_;
             if (cnum > cmax) { cmax = cnum; carg = (long long)i * RDYB_ELL_WIDTH + k; }

@@ -82,7 +82,8 @@ template <bool STRICT>
 __device__ __forceinline__ void swe_velocities(double h, double hu, double hv, double tiny_h, double ha2, double &u, double &v) {
   const bool wet = STRICT ? (h > tiny_h) : !(h < tiny_h);
   if (wet) {
-    const double r = h * swe_rcp(h * h + ha2);
+    /* h_a = 0 (the default): hu h / h^2 = hu / h, one reciprocal of h instead of the product chain (a uniform branch) */
+    const double r = ha2 == 0.0 ? swe_rcp(h) : h * swe_rcp(h * h + ha2);
     u = hu * r;
     v = hv * r;
   } else {

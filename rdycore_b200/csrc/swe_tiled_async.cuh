@@ -37,17 +37,24 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+/* try_wait suspends the thread in hardware until the phase completes or a time limit passes; without a hint that limit is short and
+ * a waiting warp keeps re-issuing SYNCS + BRA + YIELD - 11 % (Roe) to 18 % (HR) of all issued instructions of K4 in the ncu capture of
+ * round 2 (profiles/r2_ncu_full_swe_tiled_fixed_*.txt), taken from the warps that do have work.  The hint (ns) lengthens the
+ * suspension; completion still wakes the thread at once. */
+#ifndef RDYB_MBAR_SUSPEND_NS
+#define RDYB_MBAR_SUSPEND_NS 20000
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
       "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
       "@p bra DONE_%=;\n"
       "bra WAIT_%=;\n"
       "DONE_%=:\n"
       "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
+      "r"(parity), "r"((uint32_t)RDYB_MBAR_SUSPEND_NS)
       : "memory");
 }
 /* TMA 1-D bulk copy global -> shared, completion counted in bytes on `bar` */

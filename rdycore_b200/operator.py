@@ -11,7 +11,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._lib import RdybCourantDiagnostics, check, lib
+from ._lib import RdybCourantDiagnostics, RdybVertexView, check, lib
 
 GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, TILED_SPLIT = 0, 1, 2, 3, 4, 5
 
@@ -152,6 +152,25 @@ class Operator:
 
     def step_rk4(self, dt: float, nsteps: int = 1):
         check(lib().rdyb_operator_step_rk4(self._h, C.c_double(dt), C.c_int32(nsteps)))
+
+    # ---- Bradford-Sanders well balancing (libCEED semantics) ----
+    def enable_bs2002(self, mesh=None):
+        """Vertex-eta pass + the g dhv^2 / 24 edge term (SWEEtaVertex / ComputeDhv of the reference's libCEED operator)."""
+        mesh = mesh or self._keep[1]
+        z = np.ascontiguousarray(mesh.vertices()[:, 2], dtype=np.float64)
+        offs = np.ascontiguousarray(mesh.array("cell_offsets"), dtype=np.int32)
+        ids = np.ascontiguousarray(mesh.array("cell_vertex_ids"), dtype=np.int32)
+        ev = np.ascontiguousarray(mesh.array("edge_vertex_ids"), dtype=np.int32)
+        i32 = C.POINTER(C.c_int32)
+        vv = RdybVertexView(len(z), z.ctypes.data_as(C.POINTER(C.c_double)), offs.ctypes.data_as(i32), ids.ctypes.data_as(i32), ev.ctypes.data_as(i32))
+        self._bs_keep = (z, offs, ids, ev)
+        check(lib().rdyb_operator_enable_bs2002(self._h, C.byref(vv)))
+        self.num_vertices = len(z)
+
+    def eta_vertices(self) -> np.ndarray:
+        out = np.zeros(self.num_vertices)
+        check(lib().rdyb_operator_get_eta_vertices(self._h, C.c_int32(self.num_vertices), out.ctypes.data_as(C.c_void_p)))
+        return out
 
     # ---- device-side time loop ----
     def time_set(self, t: float, dt: float):

@@ -12,12 +12,12 @@ from scipy.io import netcdf_file
 SHARE = "/root/reference/share"
 HERE = os.path.dirname(os.path.abspath(__file__))
 OUT = os.path.join(HERE, "ref_fixtures")
-MESHES = ["DamBreak_grid5x10", "DamBreak_grid5x10_mixed_elements", "quad_tri_mesh", "mms_triangles_dx1", "levee", "four_mounds_60x24", "Houston1km_with_z"]
+MESHES = ["DamBreak_grid5x10", "DamBreak_grid5x10_mixed_elements", "quad_tri_mesh", "mms_triangles_dx1", "levee", "four_mounds_60x24", "Houston1km_with_z", "parabolic_bowl"]
 VECS = [
     "conditions/DamBreak_grid5x10_wetdownstream.ic.int32.bin", "conditions/DamBreak_grid5x10_wetdownstream.ic.int64.bin",
     "conditions/DamBreak_grid5x10_mixed_elements_wetdownstream.ic.int32.bin", "materials/manning_grid5x10.int32.bin",
     "materials/manning_grid5x10_mixed_elements.int32.bin", "conditions/levee_ic.int32.bin", "meshes/levee_elevation.int32.bin",
-    "conditions/four_mounds_60x24.ic.int32.bin", "materials/manning_four_mound_60x24.int32.bin", "conditions/Houston1km.ic.int32.bin",
+    "conditions/four_mounds_60x24.ic.int32.bin", "conditions/parabolic_bowl.ic.int32.bin", "materials/manning_four_mound_60x24.int32.bin", "conditions/Houston1km.ic.int32.bin",
     # forcing data: homogeneous rain and boundary series, two hourly rain rasters, unstructured rain / boundary data
     "conditions/Houston1km.rain.int32.bin", "conditions/Houston1km.bc.int32.bin", "conditions/2017-08-26:00-00.int32.bin",
     "conditions/2017-08-26:01-00.int32.bin", "conditions/simons-ss/simons_forcing_x_y.int32.bin", "conditions/simons-bc/simons_bc_x_y.int32.bin",
