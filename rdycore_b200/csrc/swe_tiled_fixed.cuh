@@ -20,17 +20,12 @@
  */
 #ifndef RDYB_SWE_TILED_FIXED_CUH
 #define RDYB_SWE_TILED_FIXED_CUH
-#ifndef RDYB_K4_DEFAULT_PRIM
-#define RDYB_K4_DEFAULT_PRIM 1 /* until the producer-warp variant (2) has been timed on the B200 */
-#endif
 #include "swe_tiled_async.cuh"
 
 /* one pipeline stage: everything the producer copies for one tile */
-template <int TC, int HM, int ME, bool HR, bool PRIMS = false>
+template <int TC, int HM, int ME, bool HR>
 struct alignas(128) FixedStage {
   static constexpr int CS = TC + HM;
-  /* PRIMS (K4 with PM == 2): the primitive state of the staged cells, written by the PRODUCER warp once the stage has landed */
-  double u[PRIMS ? CS : 2], v[PRIMS ? CS : 2], sq[(PRIMS && !HR) ? CS : 2];
   double h[CS], hu[CS], hv[CS], ia[CS];
   double z[HR ? CS : 2];            /* HR: bed elevation of the staged cells */
   double dzdx[HR ? 2 : TC], dzdy[HR ? 2 : TC];
@@ -49,7 +44,7 @@ struct alignas(128) FixedStage {
 template <int TC, int HM, int ME, bool HR, bool NOPRIM>
 struct alignas(16) FixedScratch {
   static constexpr int CS = TC + HM;
-  /* NOPRIM (PM != 0): the primitive state is computed per edge side in phase 2 or by the producer into the stage: no per-CTA scratch */
+  /* NOPRIM (PM != 0): the primitive state is computed per edge side in phase 2: no per-CTA scratch */
   double u[NOPRIM ? 2 : CS], v[NOPRIM ? 2 : CS], sq[(HR || NOPRIM) ? 2 : CS];
   /* the edge fluxes overwrite the edge geometry of the stage in place (esn <- f0, ecn <- f1, elen <- f2: an edge's thread reads
    * its geometry before it writes its flux).  HR: f1, f2 hold momentum flux + pressure correction as seen by the LEFT cell; the
@@ -57,16 +52,16 @@ struct alignas(16) FixedScratch {
 };
 
 /* PM, where the primitive state (u, v, sqrt h) of the staged cells is computed:
- *   0  a pass of the consumer warps over the staged cells + a CTA barrier (round 1's three-pass kernel);
- *   1  per edge side inside the edge pass (no pass, no barrier, but 2 evaluations per edge instead of 1.3 per cell);
- *   2  by the PRODUCER warp, which is otherwise parked: once per staged cell, into the stage, one tile ahead of the consumers,
- *      announced through prim_bar - the consumers neither compute it nor wait at a barrier for it.
- * PM != 0 also splits the barrier between the edge pass and the cell pass (flux_bar, see phase 3). */
+ *   0  a pass of the consumer warps over the staged cells + a CTA barrier (round 1's three-pass kernel, kept for A/B runs);
+ *   1  per edge side inside the edge pass (no pass, no barrier; 2 evaluations per edge instead of 1.3 per cell) - the default.
+ * PM != 0 also splits the barrier between the edge pass and the cell pass (flux_bar, see phase 3).
+ * (A third variant - the otherwise parked PRODUCER warp computing the primitives into the stage one tile ahead - was built and
+ * measured in round 2: 0.369 ms against 0.322 ms for PM 1, the single warp cannot keep up with seven consumers; removed.) */
 template <int TC, int HM, int ME, int NS, bool HR, int PM>
 struct FixedSmem {
-  FixedStage<TC, HM, ME, HR, PM == 2> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
+  FixedStage<TC, HM, ME, HR> st[NS]; /* NS-deep pipeline: dry tiles are load-latency bound, a deeper queue keeps loads in flight */
   FixedScratch<TC, HM, ME, HR, PM != 0> sc;
-  uint64_t full_bar[NS], empty_bar[NS], prim_bar[NS];
+  uint64_t full_bar[NS], empty_bar[NS];
   uint64_t flux_bar; /* FUSEP: every consumer thread arrives when its edges of the tile are done (split barrier, see phase 3) */
   double wval[16];
   int wargs[16];
@@ -132,7 +127,7 @@ template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int SRC,
 __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const FixedArgs q) {
   extern __shared__ __align__(128) char smem_raw[];
   using Smem = FixedSmem<TC, HM, ME, NS, HR, PM>;
-  constexpr bool FUSEP = PM == 1, PRODP = PM == 2, SPLITB = PM != 0;
+  constexpr bool FUSEP = PM == 1, SPLITB = PM != 0;
   Smem &S = *reinterpret_cast<Smem *>(smem_raw);
   const TiledArgs &p = q.t;
   const SweArgs &a = p.a;
@@ -140,7 +135,7 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
   constexpr int HK = (HM + 31) / 32; /* halo indices per producer lane */
   if (threadIdx.x == 0) {
     for (int s = 0; s < NS; ++s) {
-      mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], NCONS); mbar_init(&S.prim_bar[s], 32);
+      mbar_init(&S.full_bar[s], 33); mbar_init(&S.empty_bar[s], NCONS);
       /* the zero flux entry that empty cell-edge slots point at (never touched by the bulk copies: nedge <= ME - 2) */
       S.st[s].esn[ME - 1] = 0.0; S.st[s].ecn[ME - 1] = 0.0; S.st[s].elen[ME - 1] = 0.0;
       if (HR) { S.st[s].f1r[ME - 1] = 0.0; S.st[s].f2r[ME - 1] = 0.0; }
@@ -229,26 +224,6 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
         }
       }
       cp_async_arrive_noinc(bar);
-      if (PRODP) {
-        /* the consumers are busy with the previous tile and the next stage is not free yet: this warp has nothing else to do.  Wait
-         * for the copies just issued, derive u, v, sqrt(h) of every staged cell (two cells per lane and sweep: two independent
-         * dependency chains) and announce them; the consumers wait on prim_bar instead of full_bar. */
-        mbar_wait(bar, (it / NS) & 1);
-        const double tiny_p = a.tiny_h, ha2_p = a.ha2;
-        const int nst = TC + nhalo;
-        for (int x = lane; x < nst; x += 64) {
-          const int y = x + 32;
-          const bool two = y < nst;
-          const double h0 = st.h[x], h1 = two ? st.h[y] : 1.0;
-          double u0, w0, u1, w1;
-          swe_velocities<HR>(h0, st.hu[x], st.hv[x], tiny_p, ha2_p, u0, w0);
-          swe_velocities<HR>(h1, two ? st.hu[y] : 0.0, two ? st.hv[y] : 0.0, tiny_p, ha2_p, u1, w1);
-          st.u[x] = u0; st.v[x] = w0;
-          if (!HR) st.sq[x] = swe_sqrt(h0);
-          if (two) { st.u[y] = u1; st.v[y] = w1; if (!HR) st.sq[y] = swe_sqrt(h1); }
-        }
-        mbar_arrive(&S.prim_bar[s]);
-      }
       d0 = n0; d1 = n1; n0 = nn0; n1 = nn1;
 #pragma unroll
       for (int k = 0; k < HK; ++k) hidx[k] = nh[k];
@@ -266,7 +241,6 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
   int it = 0;
   for (int tile = q.tile_begin + blockIdx.x; tile < q.tile_end; tile += G, ++it) {
     const int s = it % NS;
-    if (PRODP) mbar_wait(&S.prim_bar[s], (it / NS) & 1); /* the producer has seen the stage land and has added the primitive state */
     mbar_wait(&S.full_bar[s], (it / NS) & 1);
     auto &st = S.st[s];
     const int cb = st.desc[0], ncell = st.desc[1], eo = st.desc[2], nedge = st.desc[3], nhalo = st.desc[5];
@@ -305,9 +279,6 @@ __global__ void __launch_bounds__(NCONS + 32, MINB) swe_tiled_fixed_kernel(const
           if (FUSEP) {
             if (HR) { swe_velocities<true>(hl, st.hu[l], st.hv[l], tiny, ha2, ul, vl); swe_velocities<true>(hr, st.hu[r], st.hv[r], tiny, ha2, ur, vr); }
             else { swe_edge_side(hl, st.hu[l], st.hv[l], tiny, ha2, ul, vl, sql); swe_edge_side(hr, st.hu[r], st.hv[r], tiny, ha2, ur, vr, sqr); }
-          } else if (PRODP) {
-            ul = st.u[l]; vl = st.v[l]; ur = st.u[r]; vr = st.v[r];
-            if (!HR) { sql = st.sq[l]; sqr = st.sq[r]; }
           } else {
             ul = sc.u[l]; vl = sc.v[l]; ur = sc.u[r]; vr = sc.v[r];
           }
@@ -519,19 +490,16 @@ static int fixed_launch_t(const FixedArgs &q, int ntiles, cudaStream_t stream) {
   return RDYB_SUCCESS;
 }
 
-/* which variant computes the primitive state (see FixedSmem): RDYB_K4_PRIM = 0 | 1 | 2 (A/B runs); RDYB_K4_PRIM_PASS=1 is the old
- * spelling of 0.  Default: 2 (producer warp) for the Roe kernel, 1 (per edge side) for HR, whose larger stage leaves no room for the
- * per-stage primitive arrays at three CTAs per SM. */
-static inline int fixed_prim_mode(bool hr) {
+/* which variant computes the primitive state (see FixedSmem): RDYB_K4_PRIM = 0 | 1 (A/B runs; RDYB_K4_PRIM_PASS=1 is the old spelling of 0) */
+static inline int fixed_prim_mode() {
   static int v = -2;
   if (v == -2) {
     const char *e = getenv("RDYB_K4_PRIM"), *o = getenv("RDYB_K4_PRIM_PASS");
-    v = -1;
-    if (e && e[0] >= '0' && e[0] <= '2') v = e[0] - '0';
+    v = 1;
+    if (e && (e[0] == '0' || e[0] == '1')) v = e[0] - '0';
     else if (o && o[0] == '1') v = 0;
   }
-  if (v >= 0) return (hr && v == 2) ? 1 : v;
-  return hr ? 1 : RDYB_K4_DEFAULT_PRIM;
+  return v;
 }
 template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR, int PM>
 static int fixed_launch_cfg2(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
@@ -545,12 +513,8 @@ static int fixed_launch_cfg2(const FixedArgs &q, int nt, bool xq, bool euler, bo
 }
 template <int TC, int HM, int ME, int NCONS, int NS, int MINB, bool HR>
 static int fixed_launch_cfg(const FixedArgs &q, int nt, bool xq, bool euler, bool courant, cudaStream_t stream) {
-  const int pm = fixed_prim_mode(HR);
-  if (pm == 0) return fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 0>(q, nt, xq, euler, courant, stream);
-  if constexpr (!HR) {
-    if (pm == 2) return fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 2>(q, nt, xq, euler, courant, stream);
-  }
-  return fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 1>(q, nt, xq, euler, courant, stream);
+  return fixed_prim_mode() == 0 ? fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 0>(q, nt, xq, euler, courant, stream)
+                                : fixed_launch_cfg2<TC, HM, ME, NCONS, NS, MINB, HR, 1>(q, nt, xq, euler, courant, stream);
 }
 
 /* the compiled tile shapes: {tile cells, halo capacity, edge capacity (the last entry is the zero flux), consumer threads,
