@@ -51,7 +51,7 @@ def parse_args():
     p.add_argument("--nx", type=int, default=2236, help="quads per side of one GPU's block (cells = 2*nx*ny)")
     p.add_argument("--ny", type=int, default=0)
     p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed", "warp", "split"])
-    p.add_argument("--tile", type=int, default=None, help="cells per tile (default: RDYB_TILE, else 224 = K4's shape, 128 with --second-order = K2M's)")
+    p.add_argument("--tile", type=int, default=None, help="cells per tile (default: RDYB_TILE, else 224 = K4's shape, 192 with --second-order = K3M's best)")
     p.add_argument("--no-courant", action="store_true", help="skip the per-edge Courant diagnostic (the reference always computes it)")
     p.add_argument("--e2e-steps", type=int, default=10)
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
@@ -386,7 +386,7 @@ def run_b200_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     if args.tile is None:
-        args.tile = int(os.environ.get("RDYB_TILE", "128" if args.second_order else "224"))
+        args.tile = int(os.environ.get("RDYB_TILE", "192" if args.second_order else "224"))
     px, py, nx, ny, eta0, kw = workload(args, world)
     dt = workload_dt(args, eta0)
     t_setup = time.perf_counter()

@@ -159,7 +159,7 @@ struct RdybOperator_ {
   PeerTable ptab;
   unsigned int p2p_epoch = 0;
   unsigned int *p2p_flags = nullptr; /* [RDYB_MAX_PEERS] counters raised by the neighbours, + 1 status word */
-  void *p2p_opened[3 * RDYB_MAX_PEERS];
+  void *p2p_opened[4 * RDYB_MAX_PEERS];
   int p2p_nopened = 0;
   /* fused push (K4 stores the border cells of each finished frontier tile into the neighbours itself; swe_tiled_fixed.cuh) */
   struct {
@@ -818,7 +818,7 @@ struct HaloBlob { /* <= RDYB_HALO_BLOB_BYTES */
   int32_t peer_ranks[RDYB_MAX_PEERS];
   int32_t recv_offsets[RDYB_MAX_PEERS + 1];
   int32_t send_counts[RDYB_MAX_PEERS];
-  cudaIpcMemHandle_t state[2], flags;
+  cudaIpcMemHandle_t state[3], flags; /* state[2]: the RK stage buffer (rk_y), so that RK4 stages can use the peer-memory halo too */
 };
 static_assert(sizeof(HaloBlob) <= RDYB_HALO_BLOB_BYTES, "halo blob does not fit its public size");
 
@@ -833,8 +833,10 @@ extern "C" int rdyb_operator_halo_export(RdybOperator op, int32_t rank, void *bl
   b.magic = 0x52445942u; b.rank = rank; b.n_owned = op->N; b.stride = op->stride; b.num_peers = L.num_peers;
   for (int p = 0; p < L.num_peers; ++p) { b.peer_ranks[p] = L.peer_ranks[p]; b.recv_offsets[p] = L.recv_offsets[p]; b.send_counts[p] = L.send_offsets[p + 1] - L.send_offsets[p]; }
   if (L.num_peers > 0) b.recv_offsets[L.num_peers] = L.recv_offsets[L.num_peers];
+  if (!op->rk_y) RDYB_CALL(dalloc(&op->rk_y, 3 * (size_t)op->stride));
   CU(cudaIpcGetMemHandle(&b.state[0], op->state[0]));
   CU(cudaIpcGetMemHandle(&b.state[1], op->state[1]));
+  CU(cudaIpcGetMemHandle(&b.state[2], op->rk_y));
   CU(cudaIpcGetMemHandle(&b.flags, op->p2p_flags));
   memset(blob, 0, RDYB_HALO_BLOB_BYTES);
   memcpy(blob, &b, sizeof(b));
@@ -869,14 +871,14 @@ extern "C" int rdyb_operator_halo_import(RdybOperator op, int32_t nranks, int32_
     RDYB_CHECK(q >= 0, RDYB_ERR_USER, "rank %d sends to rank %d, which does not list it as a neighbour", rank, r);
     const int nsend = L.send_offsets[p + 1] - L.send_offsets[p], nrecv_there = b.recv_offsets[q + 1] - b.recv_offsets[q];
     RDYB_CHECK(nsend == nrecv_there, RDYB_ERR_USER, "rank %d sends %d cells to rank %d, which expects %d", rank, nsend, r, nrecv_there);
-    void *ptr[3];
-    const cudaIpcMemHandle_t hs[3] = {b.state[0], b.state[1], b.flags};
-    for (int k = 0; k < 3; ++k) {
-      RDYB_CHECK(op->p2p_nopened < 3 * RDYB_MAX_PEERS, RDYB_ERR_SUP, "too many peer mappings");
+    void *ptr[4];
+    const cudaIpcMemHandle_t hs[4] = {b.state[0], b.state[1], b.flags, b.state[2]};
+    for (int k = 0; k < 4; ++k) {
+      RDYB_CHECK(op->p2p_nopened < 4 * RDYB_MAX_PEERS, RDYB_ERR_SUP, "too many peer mappings");
       CU(cudaIpcOpenMemHandle(&ptr[k], hs[k], cudaIpcMemLazyEnablePeerAccess));
       op->p2p_opened[op->p2p_nopened++] = ptr[k];
     }
-    t.state[p][0] = (double *)ptr[0]; t.state[p][1] = (double *)ptr[1];
+    t.state[p][0] = (double *)ptr[0]; t.state[p][1] = (double *)ptr[1]; t.state[p][2] = (double *)ptr[3];
     t.flag[p] = (unsigned int *)ptr[2] + q;
     t.stride[p] = b.stride; t.ghost0[p] = b.n_owned + b.recv_offsets[q];
     t.send_begin[p] = L.send_offsets[p];
@@ -941,6 +943,19 @@ static int p2p_wait(RdybOperator op) {
                                             reinterpret_cast<int *>(op->p2p_flags + RDYB_MAX_PEERS));
   LAUNCHED();
   CU(cudaGetLastError());
+  return RDYB_SUCCESS;
+}
+
+/* RHS of a stage vector that lives in one of the three peer-mapped buffers (state[0], state[1], rk_y): border cells go straight into
+ * the neighbours' ghost slots of the SAME buffer over NVLink, the interior cells run meanwhile, the frontier cells after the
+ * neighbours' counters have arrived.  Safe while consecutive evaluations use different buffers: a rank starts the frontier of
+ * evaluation k only after its neighbours have pushed their data of evaluation k, i.e. have finished evaluation k - 1, so nobody
+ * is more than one evaluation ahead and a push never lands in a buffer its receiver still reads (step_rk4 orders its stages so). */
+static int rhs_pass_p2p(RdybOperator op, double *in, int bufidx, double *out, double dt) {
+  RDYB_CALL(p2p_push(op, in, bufidx));
+  RDYB_CALL(launch_cells(op, in, out, dt, false, 0, op->NI, 0));
+  RDYB_CALL(p2p_wait(op));
+  RDYB_CALL(launch_cells(op, in, out, dt, false, op->NI, op->N, op->ncblocks_interior));
   return RDYB_SUCCESS;
 }
 
@@ -1524,20 +1539,26 @@ extern "C" int rdyb_operator_step_rk4(RdybOperator op, double dt, int32_t nsteps
   const double bw[4] = {1.0 / 6.0, 1.0 / 3.0, 1.0 / 3.0, 1.0 / 6.0};
   const int g = grid_for(op->N, 256);
   CU(cudaEventRecord(op->ev_t0, op->stream));
+  /* the stage vectors alternate between the spare state buffer and rk_y, so that consecutive RHS evaluations never read the same
+   * buffer: U, S, R, S | U, S, R, S ... - what the peer-memory halo needs (rhs_pass_p2p); harmless on one GPU */
+  const bool p2p = op->p2p && !op->recon && !getenv("RDYB_RK4_NCCL");
   for (int32_t s = 0; s < nsteps; ++s) {
     double *U = op->state[op->cur];
     for (int i = 0; i < 4; ++i) {
       double *Y = U;
+      int ybuf = op->cur;
       if (i > 0) {
-        stage_axpy_kernel<<<g, 256, 0, op->stream>>>(U, op->rk_k[i - 1], dt * a[i], op->rk_y, op->N, op->stride);
+        Y = (i & 1) ? op->state[op->cur ^ 1] : op->rk_y;
+        ybuf = (i & 1) ? (op->cur ^ 1) : 2;
+        stage_axpy_kernel<<<g, 256, 0, op->stream>>>(U, op->rk_k[i - 1], dt * a[i], Y, op->N, op->stride);
         LAUNCHED();
         CU(cudaGetLastError());
-        Y = op->rk_y;
       }
       /* OperatorRHSFunction resets the diagnostics in every call (src/rdysetup.c:1136), so after TSSolve they hold the LAST stage's
        * Courant number only: clear the slots before the final stage of the final step */
       if (i == 3 && s == nsteps - 1 && op->opt_courant) RDYB_CALL(rdyb_operator_reset_diagnostics(op));
-      RDYB_CALL(rhs_pass(op, Y, op->rk_k[i], dt, false));
+      if (p2p) RDYB_CALL(rhs_pass_p2p(op, Y, ybuf, op->rk_k[i], dt));
+      else RDYB_CALL(rhs_pass(op, Y, op->rk_k[i], dt, false));
     }
     rk4_combine_kernel<<<g, 256, 0, op->stream>>>(U, op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], dt * bw[0], dt * bw[1], dt * bw[2],
                                                   dt * bw[3], op->N, op->stride);

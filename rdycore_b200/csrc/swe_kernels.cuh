@@ -381,7 +381,7 @@ __global__ void halo_unpack_kernel(const double *__restrict__ buf, double *__res
  * neighbour's flag word; the neighbour's stream waits for that counter before its frontier cells run. */
 #define RDYB_MAX_PEERS 8
 struct PeerTable {
-  double *state[RDYB_MAX_PEERS][2];   /* neighbour's two state buffers (ping-pong), mapped through CUDA IPC */
+  double *state[RDYB_MAX_PEERS][3];   /* neighbour's two state buffers (ping-pong) and its RK stage buffer, mapped through CUDA IPC */
   unsigned int *flag[RDYB_MAX_PEERS]; /* the word in the neighbour's flag array that belongs to this rank */
   int32_t stride[RDYB_MAX_PEERS];     /* neighbour's leading dimension */
   int32_t ghost0[RDYB_MAX_PEERS];     /* neighbour's device index of the first ghost cell it receives from this rank */

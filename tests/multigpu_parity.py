@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--kernel", type=int, default=3)
     ap.add_argument("--tile", type=int, default=224)
     ap.add_argument("--p2p", action="store_true", help="peer-memory halo (CUDA IPC over NVLink) instead of NCCL send/recv")
+    ap.add_argument("--rk4", action="store_true", help="classical RK4 instead of forward Euler: with --p2p the four stage vectors of a step travel over the "
+                    "peer-memory halo (rdyb_operator_step_rk4: stage buffers alternate so that consecutive RHS evaluations never share one)")
     ap.add_argument("--mixed-paths", action="store_true", help="momentum sources on rank 0's cells only: rank 0 leaves the fused-push K4 path "
                     "(general kernel + push kernel) while the other ranks stay on it; the epoch accounting must keep them in step")
     ap.add_argument("--max-ctas", type=int, default=0, help="cap the persistent grid: every CTA walks many tiles (frontier and interior), the bench regime")
@@ -80,10 +82,11 @@ def main():
     m0 = torch.tensor([op.mass()], dtype=torch.float64, device="cuda")
     # three calls: each one primes the neighbours again, and the epochs of the fused push carry over between calls
     n1 = (args.steps - 1) // 2
-    op.step_euler(serial.dt, n1)
-    op.step_euler(serial.dt, args.steps - 1 - n1)
+    step = (lambda n: op.step_rk4(2 * serial.dt, n)) if args.rk4 else (lambda n: op.step_euler(serial.dt, n))
+    step(n1)
+    step(args.steps - 1 - n1)
     op.reset_diagnostics()  # the oracle's Courant diagnostic covers its last RHS evaluation only
-    op.step_euler(serial.dt, 1)
+    step(1)
     op.synchronize()
     u = op.get_state()
     m1 = torch.tensor([op.mass()], dtype=torch.float64, device="cuda")
@@ -106,7 +109,10 @@ def main():
         from util import assert_state_close, make_oracle
 
         oracle = make_oracle(serial)
-        oracle.step_euler(serial.dt, args.steps)
+        if args.rk4:
+            oracle.step_rk4(2 * serial.dt, args.steps)
+        else:
+            oracle.step_euler(serial.dt, args.steps)
         sg = serial.mesh.array("cell_global_ids")[serial.mesh.array("owned_to_local")]
         u_ref_by_gid = np.zeros((int(sg.max()) + 1, 3))
         u_ref_by_gid[sg] = oracle.array("u_global").reshape(-1, 3)

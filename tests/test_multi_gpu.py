@@ -73,6 +73,15 @@ def test_two_ranks_on_different_step_paths_stay_in_step():
     _run(2, ["--p2p", "--kernel", "3", "--tile", "224", "--steps", "80", "--mixed-paths"], 29587)
 
 
+@pytest.mark.parametrize("kernel,tile", [(0, 0), (3, 224)])
+def test_two_ranks_rk4_stages_over_the_peer_memory_halo(kernel, tile):
+    """TSRK4 on a partitioned mesh without NCCL on the data path: each of the four RHS evaluations of a step pushes the border cells
+    of its stage vector into the neighbour's ghost slots of the same (peer-mapped) buffer."""
+    if _ngpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _run(2, ["--p2p", "--rk4", "--kernel", str(kernel), "--tile", str(tile), "--steps", "40"], 29575 + kernel)
+
+
 def test_four_ranks_fused_push_many_tiles_per_cta():
     if _ngpus() < 4:
         pytest.skip("needs 4 GPUs")
