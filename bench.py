@@ -50,7 +50,7 @@ def parse_args():
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--nx", type=int, default=2236, help="quads per side of one GPU's block (cells = 2*nx*ny)")
     p.add_argument("--ny", type=int, default=0)
-    p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed", "warp", "split"])
+    p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed"])
     p.add_argument("--tile", type=int, default=None, help="cells per tile (default: RDYB_TILE, else 224 = K4's shape, 192 with --second-order = K3M's best)")
     p.add_argument("--no-courant", action="store_true", help="skip the per-edge Courant diagnostic (the reference always computes it)")
     p.add_argument("--e2e-steps", type=int, default=10)
@@ -370,7 +370,7 @@ def run_b200_arm(args):
 
     from rdycore_b200 import cases
     from rdycore_b200._lib import lib
-    from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP, Operator, kernel_launch_count
+    from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, Operator, kernel_launch_count
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -395,8 +395,8 @@ def run_b200_arm(args):
         case.config.reconstruction = cases.MUSCL_MINMOD
     halo = case.mesh.halo() if world > 1 else None
     op = Operator.from_case(case, device=local_rank, halo=halo)
-    kernel = {"auto": TILED_FIXED, "gather": GATHER, "tiled": TILED, "async": TILED_ASYNC, "fixed": TILED_FIXED, "warp": WARP, "split": TILED_SPLIT}[args.kernel]
-    kernel_name = {GATHER: "gather", TILED: "tiled", TILED_ASYNC: "tiled_async", TILED_FIXED: "tiled_fixed", WARP: "warp", TILED_SPLIT: "tiled_split"}[kernel]
+    kernel = {"auto": TILED_FIXED, "gather": GATHER, "tiled": TILED, "async": TILED_ASYNC, "fixed": TILED_FIXED}[args.kernel]
+    kernel_name = {GATHER: "gather", TILED: "tiled", TILED_ASYNC: "tiled_async", TILED_FIXED: "tiled_fixed"}[kernel]
     op.set_kernel(kernel, args.tile)
     if args.max_ctas:
         op.set_max_ctas(args.max_ctas)

@@ -148,7 +148,7 @@ int rdyb_operator_set_options(RdybOperator op, int courant, int flux_divergence,
 
 /* kernel selection: kind 0 = K1 cell-centric gather (default), 1 = K2 shared-memory tiles of `tile_cells` cells,
  * 2 = K3 persistent bulk-async-staged tiles, 3 = K4 (K3 with compile-time tile shapes, tuned for tile_cells 224; shapes that do
- * not fit run K3), 4 = K5 one 32-cell mini-tile per warp, 5 = K6 K4's pipeline without a producer warp.  With
+ * not fit run K3).  With
  * config.reconstruction != 0 (second order) every kind >= 1 runs K2M, the tiled MUSCL kernel (tuned for tile_cells 128), kind 0
  * the cell-centric MUSCL gather; rdyb_operator_kernel_info reports which kernel the last launch ran. */
 int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells);

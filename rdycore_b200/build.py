@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librdyb200.so")
 OBJDIR = os.path.join(HERE, "build")
 
-C_SOURCES = ["rdyb_error.c", "host_mesh.c", "device_layout.c", "warp_layout.c", "petsc_operator_b200.c", "rdy_driver.c", "io_formats.c"]
+C_SOURCES = ["rdyb_error.c", "host_mesh.c", "device_layout.c", "petsc_operator_b200.c", "rdy_driver.c", "io_formats.c"]
 CU_SOURCES = ["swe_device.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

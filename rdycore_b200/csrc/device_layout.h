@@ -91,33 +91,6 @@ typedef struct {
   int64_t   edge_off_plane;
 } RdybTiledLayout;
 
-/* warp-tile layout (kernel "warp", K5): every tile of tile_cells cells is cut into mini-tiles of 32 consecutive cells, one per
- * consumer warp.  A mini-tile lists its own edges (interior first, boundary edges last) with WARP-LOCAL endpoints
- * (0..31 own cells, 32+k the k-th entry of its halo list) and the staged-array index of each of its halo cells, so that a
- * warp computes its 32 cells without any CTA-wide barrier.  Edges between two mini-tiles are listed (and evaluated) by both. */
-#define RDYB_WARP_CELLS 32
-typedef struct {
-  int32_t tile_cells;         /* multiple of 64 */
-  int32_t num_tiles, num_interior_tiles;
-  int32_t max_halo;           /* per tile: cells staged from outside the tile */
-  int32_t max_tile_edges;     /* per tile: sum of its mini-tiles' edge counts */
-  int32_t max_tile_whalo;     /* per tile: sum of its mini-tiles' halo counts */
-  int32_t max_warp_edges, max_warp_halo; /* per mini-tile */
-  int32_t *tile_desc;         /* [8*num_tiles] {cell_begin, ncell, edge_begin, nedge, halo_begin, nhalo, whalo_begin, nwhalo}; begins padded to 8 */
-  int32_t *halo_cells;        /* device indices of the non-tile cells a tile stages (at staged index tile_cells + k) */
-  uint16_t *wdesc;            /* [num_tiles][tile_cells/32][4] {edge_begin (in tile), nint | nbnd << 8, whalo_begin (in tile), nwhalo} */
-  uint16_t *whalo;            /* staged index of each mini-tile halo cell */
-  uint16_t *edge_lr;          /* left | right << 8, warp-local; right == 0xFF => boundary edge, see edge_bidx */
-  int32_t  *edge_bidx;        /* flattened boundary-edge index or -1 */
-  int32_t  *edge_id, *edge_cell; /* host only: local edge id and the device cell the Courant diagnostic reports */
-  double   *edge_sn, *edge_cn, *edge_len;
-  uint8_t  *cell_edges;       /* [RDYB_ELL_WIDTH*stride] slot-major: mini-tile edge index | 0x80 if the cell is the right cell; 0xFF empty */
-  int64_t   total_edges, total_halo, total_whalo;
-} RdybWarpLayout;
-
-int  rdyb_warp_layout_build(const RdybLayout *layout, int32_t tile_cells, RdybWarpLayout *out);
-void rdyb_warp_layout_free(RdybWarpLayout *w);
-
 int  rdyb_layout_build(const RdybMeshView *mesh, int32_t num_boundaries, const RdybBoundaryView *boundaries, const RdybHaloView *halo,
                        int reorder, RdybLayout *out);
 int  rdyb_layout_build_muscl(const RdybMeshView *mesh, RdybLayout *layout);

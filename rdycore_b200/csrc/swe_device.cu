@@ -22,10 +22,8 @@
 #include "swe_tiled.cuh"
 #include "swe_tiled_async.cuh"
 #include "swe_tiled_fixed.cuh"
-#include "swe_tiled_split.cuh"
 #include "swe_tiled_muscl.cuh"
 #include "swe_tiled_muscl_async.cuh"
-#include "swe_warp.cuh"
 
 static std::atomic<int64_t> g_launches{0};
 static std::atomic<int64_t> g_host_syncs{0}; /* host waits for the device (stream / event synchronisations) since load */
@@ -118,11 +116,7 @@ struct RdybOperator_ {
   /* tiled-kernel device arrays */
   TiledDev td;
   bool has_tiled = false;
-  /* warp-tile kernel (K5) */
-  RdybWarpLayout WL;
-  WarpDev wd;
   const char *last_kernel = "none";
-  bool has_warp = false, warp_used = false; /* warp_used: the last launch ran K5 (not a fallback) */
   /* device-side time loop (rdyb_operator_advance_device): control block, its pinned mirror, the instantiated graph */
   struct {
     AdvCtl *ctl = nullptr, *mirror = nullptr;
@@ -147,9 +141,7 @@ struct RdybOperator_ {
   int max_ctas = 0; /* cap on the grid of the persistent kernels (0 = none): rdyb_operator_set_max_ctas */
   long long p2p_timeout_cycles = 40000000000ll; /* in-kernel / wait-kernel neighbour time-out (~20 s; RDYB_P2P_TIMEOUT_S) */
   unsigned long long *wait_cycles = nullptr; /* [1] clock64() ticks the producers of this rank spent waiting for neighbours (sum over CTAs) */
-  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3),
-                          4 = one 32-cell mini-tile per warp (K5; falls back to K4 / K3), 5 = K4's pipeline with the work split across
-                          threads and no producer warp (K6; falls back to K4 / K3) */
+  int kernel_kind = 0; /* 0 = gather (K1), 1 = tiled (K2), 2 = tiled + bulk-async staging (K3), 3 = K3 with compile-time tile shapes (K4; falls back to K3) */
   /* options */
   bool opt_courant = true, opt_fdiv = false, opt_prim = false, opt_bflux = false;
   bool mom_src = false; /* any momentum external source set */
@@ -247,8 +239,6 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
   if (op->pipe.s_in) cudaStreamDestroy(op->pipe.s_in);
   if (op->pipe.s_out) cudaStreamDestroy(op->pipe.s_out);
   tiled_dev_free(&op->td);
-  warp_dev_free(&op->wd);
-  rdyb_warp_layout_free(&op->WL);
   if (op->ev_pack) cudaEventDestroy(op->ev_pack);
   if (op->ev_halo) cudaEventDestroy(op->ev_halo);
   if (op->ev_t0) cudaEventDestroy(op->ev_t0);
@@ -345,8 +335,6 @@ extern "C" int rdyb_operator_create(const RdybConfig *config, const RdybMeshView
   memset(&op->L, 0, sizeof(op->L));
   memset(&op->T, 0, sizeof(op->T));
   memset(&op->td, 0, sizeof(op->td));
-  memset(&op->WL, 0, sizeof(op->WL));
-  memset(&op->wd, 0, sizeof(op->wd));
   memset(&op->ptab, 0, sizeof(op->ptab));
   int ierr = operator_create_impl(op, config, mesh, nb, bnd, halo, device, cuda_stream);
   if (ierr) {
@@ -401,10 +389,10 @@ static int ensure_courant_slots(RdybOperator op, int32_t n) {
   CU(cudaMemset(op->carg, 0xff, sizeof(long long) * (size_t)n));
   return RDYB_SUCCESS;
 }
-/* kernel selection: 0 = K1 gather, 1 = K2 tiled (built on first use) */
+/* kernel selection: 0 = K1 gather, 1 = K2 tiled, 2 = K3 bulk-async staging, 3 = K4 compile-time tile shapes (the tiled layout is built on first use) */
 extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t tile_cells) {
   RDYB_CHECK(op, RDYB_ERR_ARG, "NULL operator");
-  RDYB_CHECK(kind >= 0 && kind <= 5, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
+  RDYB_CHECK(kind >= 0 && kind <= 3, RDYB_ERR_ARG, "unknown kernel kind %d", kind);
   CU(cudaSetDevice(op->device));
   if (kind >= 1) {
     if (op->has_tiled && op->T.tile_cells != tile_cells) {
@@ -424,18 +412,6 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
         RDYB_CALL(upload(&op->t_edge_off, op->T.edge_off, 4 * (size_t)op->T.edge_off_plane));
       }
       op->has_tiled = true;
-    }
-  }
-  if (kind == 4) {
-    if (op->has_warp && op->WL.tile_cells != tile_cells) {
-      warp_dev_free(&op->wd);
-      rdyb_warp_layout_free(&op->WL);
-      op->has_warp = false;
-    }
-    if (!op->has_warp) {
-      RDYB_CALL(rdyb_warp_layout_build(&op->L, tile_cells, &op->WL));
-      RDYB_CALL(warp_dev_upload(&op->WL, &op->L, &op->wd));
-      op->has_warp = true;
     }
   }
   op->kernel_kind = kind;
@@ -713,12 +689,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
       fw.push_epoch = op->p2p_epoch + 1; fw.push_flag = op->ptab.flag;
     }
     const FixedWait *wait = op->wait_in_kernel ? &fw : nullptr;
-    op->warp_used = op->kernel_kind == 4 && op->has_warp && warp_applicable(op->WL, t);
-    if (op->warp_used) { op->last_kernel = "swe_warp_kernel (K5)"; RDYB_CALL(warp_launch(op->wd, op->WL, op->cfg, t, op->NI, euler, op->opt_courant, op->stream)); }
-    else if (op->kernel_kind == 5 && tiled_split_applicable(op->td, op->T.tile_cells, mh, me, t)) {
-      if (interior || op->NI == 0) op->last_kernel = "swe_tiled_split_kernel (K6)";
-      RDYB_CALL(tiled_split_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, op->stream));
-    } else if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T.tile_cells, mh, me, t)) {
+    if (op->kernel_kind >= 3 && tiled_fixed_applicable(op->T.tile_cells, mh, me, t)) {
       if (begin < op->NI || op->NI == 0) op->last_kernel = "swe_tiled_fixed_kernel (K4)";
       RDYB_CALL(tiled_fixed_launch(op->td, op->T, op->cfg, t, op->NI, euler, op->opt_courant, mh, me, op->stream, wait));
     } else if (op->kernel_kind >= 2) {
@@ -1117,7 +1088,7 @@ extern "C" int rdyb_operator_apply_host(RdybOperator op, double dt, const double
   RDYB_CHECK(op && u_local && f_global, RDYB_ERR_ARG, "NULL argument");
   CU(cudaSetDevice(op->device));
   RDYB_CALL(adv_resolve(op));
-  if ((op->kernel_kind == 2 || op->kernel_kind == 3 || op->kernel_kind == 5) && op->has_tiled && !op->recon) { /* K3 / K4: chunked, overlapped copies */
+  if ((op->kernel_kind == 2 || op->kernel_kind == 3) && op->has_tiled && !op->recon) { /* K3 / K4: chunked, overlapped copies */
     if (!op->pipe.built || op->pipe.tile_cells != op->T.tile_cells) RDYB_CALL(pipe_build(op));
     if (op->pipe.usable) return apply_host_pipelined(op, dt, u_local, f_global);
   }
@@ -1600,11 +1571,7 @@ extern "C" int rdyb_operator_get_courant(RdybOperator op, RdybCourantDiagnostics
   long long arg = -1;
   for (size_t i = 0; i < v.size(); ++i)
     if (v[i] > d->max_courant_num || (v[i] == d->max_courant_num && a[i] >= 0 && (arg < 0 || a[i] < arg))) { d->max_courant_num = v[i]; arg = a[i]; }
-  if (arg >= 0 && op->kernel_kind == 4 && op->has_warp && op->warp_used) {
-    /* warp kernel: arg = global mini-tile-edge index */
-    d->global_edge_id = op->WL.edge_id[arg];
-    d->global_cell_id = op->L.dev_to_local[op->WL.edge_cell[arg]];
-  } else if (arg >= 0 && op->courant_arg_tiled && op->has_tiled) {
+  if (arg >= 0 && op->courant_arg_tiled && op->has_tiled) {
     /* tiled kernel: arg = global tile-edge index */
     d->global_edge_id = op->T.edge_id[arg];
     d->global_cell_id = op->L.dev_to_local[op->T.edge_cell[arg]];

@@ -26,7 +26,6 @@ struct TiledDev {
   uint32_t *edge_lr;
   double *edge_sn, *edge_cn, *edge_len;
   uint16_t *cell_edges;
-  int32_t *tile_rec; /* K6: per tile {tile_desc[8], halo cell indices[80]} */
   /* optional launch order (pipelined host-Vec apply): positions [sub_begin, sub_end) of `order` name the tiles to run */
   const int32_t *order;
   int32_t sub_begin, sub_end;
@@ -41,7 +40,6 @@ struct TiledArgs {
   const double *__restrict__ edge_sn, *__restrict__ edge_cn, *__restrict__ edge_len;
   const uint16_t *__restrict__ cell_edges;
   const int32_t *__restrict__ tile_order; /* NULL: tiles run in index order; else launch position -> tile (K3, K4) */
-  const int32_t *__restrict__ tile_rec;   /* K6 tile records */
   int32_t tile0;      /* first tile of this launch */
   int32_t max_cells;  /* shared-memory capacities */
   int32_t max_staged; /* tile cells + halo cells */
@@ -202,7 +200,7 @@ __global__ void __launch_bounds__(RDYB_TILE_THREADS, 2) swe_tiled_kernel(const T
 
 /* ---------------- host side ---------------- */
 static inline void tiled_dev_free(TiledDev *d) {
-  void *ptrs[] = {d->tile_desc, d->tile_cell_begin, d->halo_offsets, d->halo_cells, d->edge_offsets, d->edge_bidx, d->edge_lr, d->edge_sn, d->edge_cn, d->edge_len, d->cell_edges, d->tile_rec};
+  void *ptrs[] = {d->tile_desc, d->tile_cell_begin, d->halo_offsets, d->halo_cells, d->edge_offsets, d->edge_bidx, d->edge_lr, d->edge_sn, d->edge_cn, d->edge_len, d->cell_edges};
   for (void *q : ptrs)
     if (q) cudaFree(q);
   memset(d, 0, sizeof(*d));
@@ -230,25 +228,11 @@ static inline int tiled_dev_upload(const RdybTiledLayout *T, const RdybLayout *L
   RDYB_CALL(tiled_up(&d->edge_cn, T->edge_cn, ne));
   RDYB_CALL(tiled_up(&d->edge_len, T->edge_len, ne));
   RDYB_CALL(tiled_up(&d->cell_edges, T->cell_edges, (size_t)RDYB_ELL_WIDTH * (size_t)L->stride));
-  if (nt > 0) { /* K6 tile records (swe_tiled_split.cuh): descriptor + halo list, one bulk copy per tile; a range whose tiles have more
-                 * than 80 halo cells never runs K6 (tiled_split_applicable), so longer lists are simply cut */
-    const size_t ri = 88;
-    int32_t *rec = (int32_t *)calloc(nt * ri, sizeof(int32_t));
-    if (!rec) return rdyb_fail(RDYB_ERR_MEM, "out of host memory (tile records)");
-    for (size_t t = 0; t < nt; ++t) {
-      const int32_t *dsc = T->tile_desc + 8 * t;
-      memcpy(rec + t * ri, dsc, 8 * sizeof(int32_t));
-      memcpy(rec + t * ri + 8, T->halo_cells + dsc[4], (size_t)(dsc[5] < 80 ? dsc[5] : 80) * sizeof(int32_t));
-    }
-    const int rc = tiled_up(&d->tile_rec, rec, nt * ri);
-    free(rec);
-    RDYB_CALL(rc);
-  }
   return RDYB_SUCCESS;
 }
 
 
-/* ---------------- grid of the persistent kernels (K3, K4, K5, K6, K3M) ----------------
+/* ---------------- grid of the persistent kernels (K3, K4, K3M) ----------------
  * One CTA per resident slot: SMs x CTAs/SM, cached PER DEVICE (cudaFuncSetAttribute and the occupancy are per device; an
  * operator may be created on any device of the process).  Caps, for experiments and tests:
  *   RDYB_CTAS_PER_SM=n   fewer resident CTAs per SM;

@@ -13,7 +13,7 @@ import numpy as np
 
 from ._lib import RdybCourantDiagnostics, RdybVertexView, check, lib
 
-GATHER, TILED, TILED_ASYNC, TILED_FIXED, WARP, TILED_SPLIT = 0, 1, 2, 3, 4, 5
+GATHER, TILED, TILED_ASYNC, TILED_FIXED = 0, 1, 2, 3
 
 
 def _f64(a):

@@ -5,7 +5,7 @@
 set -e
 cd "$(dirname "$0")/../.."
 mkdir -p /tmp/asan
-for f in rdyb_error host_mesh device_layout warp_layout petsc_operator_b200 rdy_driver io_formats; do
+for f in rdyb_error host_mesh device_layout petsc_operator_b200 rdy_driver io_formats; do
   gcc -std=c11 -O1 -g -fsanitize=address,undefined -fno-omit-frame-pointer -fPIC -Iinclude -Irdycore_b200/csrc -I/usr/local/cuda/include \
       -c rdycore_b200/csrc/$f.c -o /tmp/asan/$f.o
 done

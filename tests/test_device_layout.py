@@ -129,7 +129,7 @@ NO_EDGE = -2**31
 @pytest.mark.parametrize("partitioned", [False, True])
 @pytest.mark.parametrize("tile_cells", [128, 224])
 def test_tiled_layout_invariants(tile_cells, partitioned, schedule, monkeypatch):
-    """What the tiled kernels (K2-K6, K2M) assume about a tile: padded slices, a sorted halo outside the tile, edges with at least one
+    """What the tiled kernels (K2-K4, K2M, K3M) assume about a tile: padded slices, a sorted halo outside the tile, edges with at least one
     tile cell, per-cell edge slots that mirror the ELL slots (same edge, same side, same geometry, same order), short frontier tiles."""
     if schedule:  # the opt-in bank-aware edge order permutes a tile's edges; every invariant must survive it
         monkeypatch.setenv("RDYB_EDGE_SCHEDULE", "1")
@@ -156,7 +156,7 @@ def test_tiled_layout_invariants(tile_cells, partitioned, schedule, monkeypatch)
             assert eo % 4 == 0 and ho % 4 == 0 and 0 < ncell <= TC and cb == covered
             covered += ncell
             assert (cb + ncell <= NI) if interior else (cb >= NI)
-            # the producer warps fetch every per-tile slice with bulk copies rounded up to 16 bytes (K3, K4, K6, K3M): the rounded
+            # the producer warps fetch every per-tile slice with bulk copies rounded up to 16 bytes (K3, K4, K3M): the rounded
             # slices must stay inside the arrays, and start 16-byte aligned for every element size in use (2, 4, 8 bytes)
             assert cb % 8 == 0 and cb + ((ncell + 7) & ~7) <= S
             assert eo + ((nedge + 3) & ~3) <= T.total_edges and ho + nhalo <= T.total_halo
@@ -270,83 +270,4 @@ def test_cell_centric_layout_mirrors_the_mesh(which):
             assert np.array_equal(d2l[N:], h["recv_cells"])
             assert np.array_equal(d2l[_np(L.send_cells, h["send_offsets"][-1])], h["send_cells"])
     finally:
-        lib().rdyb_layout_free(C.byref(L))
-
-
-class RdybWarpLayout(C.Structure):  # device_layout.h
-    _fields_ = [("tile_cells", C.c_int32), ("num_tiles", C.c_int32), ("num_interior_tiles", C.c_int32), ("max_halo", C.c_int32),
-                ("max_tile_edges", C.c_int32), ("max_tile_whalo", C.c_int32), ("max_warp_edges", C.c_int32), ("max_warp_halo", C.c_int32),
-                ("tile_desc", c_i32p), ("halo_cells", c_i32p), ("wdesc", c_u16p), ("whalo", c_u16p), ("edge_lr", c_u16p), ("edge_bidx", c_i32p),
-                ("edge_id", c_i32p), ("edge_cell", c_i32p), ("edge_sn", c_f64p), ("edge_cn", c_f64p), ("edge_len", c_f64p),
-                ("cell_edges", C.POINTER(C.c_uint8)), ("total_edges", C.c_int64), ("total_halo", C.c_int64), ("total_whalo", C.c_int64)]
-
-
-@pytest.mark.parametrize("which", ["quads", "triangles_rank1"])
-def test_warp_layout_invariants(which):
-    """K5's mini-tiles (rdyb_warp_layout_build): every ELL slot of a cell maps to an edge of ITS 32-cell mini-tile with the same side,
-    geometry and neighbour — reached through the mini-tile halo list, the tile's staged index and the tile halo — interior edges listed
-    before boundary edges, 8-entry aligned tile slices."""
-    halo = None
-    if which == "quads":
-        case = cases.dam_break_quads(nx=30, ny=22)
-    else:
-        case = cases.floodplain(nx=44, ny=30, eta0=8.0, px=2, py=1, rank=1)
-        halo = case.mesh.halo()
-    view = case.mesh.view()
-    arr, nb = case.boundary_views()
-    L, Wl = RdybLayout(), RdybWarpLayout()
-    check(lib().rdyb_layout_build(C.byref(view), C.c_int32(nb), arr, C.byref(halo) if halo is not None else None, C.c_int(1), C.byref(L)))
-    check(lib().rdyb_warp_layout_build(C.byref(L), C.c_int32(256), C.byref(Wl)))
-    try:
-        S, W, TC, N = L.stride, L.width, Wl.tile_cells, L.n_owned
-        desc = _np(Wl.tile_desc, 8 * Wl.num_tiles).reshape(-1, 8)
-        wdesc = _np(Wl.wdesc, 4 * (TC // 32) * Wl.num_tiles).reshape(Wl.num_tiles, TC // 32, 4)
-        ne = Wl.total_edges
-        lr, bidx, eid = _np(Wl.edge_lr, ne), _np(Wl.edge_bidx, ne), _np(Wl.edge_id, ne)
-        esn, ecn, elen = _np(Wl.edge_sn, ne), _np(Wl.edge_cn, ne), _np(Wl.edge_len, ne)
-        whalo, halo_cells = _np(Wl.whalo, Wl.total_whalo), _np(Wl.halo_cells, Wl.total_halo)
-        cell_edges = _np(Wl.cell_edges, 4 * S).reshape(4, S)
-        nbr, slen = _np(L.ell_nbr, 4 * S).reshape(4, S), _np(L.ell_slen, 4 * S).reshape(4, S)
-        lsn, lcn, ledge = _np(L.ell_sn, 4 * S).reshape(4, S), _np(L.ell_cn, 4 * S).reshape(4, S), _np(L.ell_edge, 4 * S).reshape(4, S)
-        covered = 0
-        for t, (cb, ncell, e0t, net, h0, nth, w0t, nwt) in enumerate(desc):
-            assert e0t % 8 == 0 and h0 % 8 == 0 and w0t % 8 == 0 and cb == covered and 0 < ncell <= TC
-            covered += ncell
-            for w in range(TC // 32):
-                eb, counts, wb_, nwh = (int(x) for x in wdesc[t, w])
-                nint, nbnd = counts & 0xFF, counts >> 8
-                wb, we = cb + 32 * w, min(cb + 32 * w + 32, cb + ncell)
-                if wb >= cb + ncell:
-                    assert counts == 0 and nwh == 0
-                    continue
-                g0 = e0t + eb
-                assert np.all(bidx[g0:g0 + nint] == -1) and np.all(bidx[g0 + nint:g0 + nint + nbnd] >= 0)  # interior edges first
-                used = np.zeros(nint + nbnd, bool)
-                for i in range(wb, we):
-                    for k in range(W):
-                        ce = int(cell_edges[k, i])
-                        if nbr[k, i] == NO_EDGE:
-                            assert ce == 0xFF
-                            continue
-                        e, right = ce & 0x7F, bool(ce & 0x80)
-                        assert e < nint + nbnd and right == (slen[k, i] > 0)
-                        used[e] = True
-                        g = g0 + e
-                        l, r = int(lr[g]) & 0xFF, int(lr[g]) >> 8
-                        assert (r if right else l) == i - wb
-                        other = l if right else r
-                        if nbr[k, i] < 0:
-                            assert other == 0xFF and bidx[g] == -(nbr[k, i] + 1)
-                        else:
-                            if other < 32:
-                                dev = wb + other
-                            else:
-                                staged = int(whalo[w0t + wb_ + other - 32])  # index in the tile's staged arrays
-                                dev = cb + staged if staged < TC else halo_cells[h0 + staged - TC]
-                            assert dev == nbr[k, i]
-                        assert eid[g] == ledge[k, i] and esn[g] == lsn[k, i] and ecn[g] == lcn[k, i] and elen[g] == abs(slen[k, i])
-                assert used.all()
-        assert covered == N
-    finally:
-        lib().rdyb_warp_layout_free(C.byref(Wl))
         lib().rdyb_layout_free(C.byref(L))

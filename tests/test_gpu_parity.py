@@ -9,19 +9,17 @@ import pytest
 
 from rdycore_b200 import cases
 from rdycore_b200.mesh import HostMesh
-from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP, Operator
+from rdycore_b200.operator import GATHER, TILED, TILED_ASYNC, TILED_FIXED, Operator
 
 from util import REL_TOL, assert_state_close, celerity_momentum, make_oracle, state_error
 
 pytestmark = pytest.mark.gpu
 
-WARP128 = (WARP, 128)  # K5 with 128-cell staged tiles and a 4-deep pipeline
 FIXED224 = (TILED_FIXED, 224)  # K4 shape with 7 consumer warps and three CTAs per SM (the bench default)
-SPLIT224 = (TILED_SPLIT, 224)  # K6: K4's pipeline, work split across 384 threads, no producer warp
-KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, FIXED224, SPLIT224, WARP, WARP128]
+KERNELS = [GATHER, TILED, TILED_ASYNC, TILED_FIXED, FIXED224]
 
 
-PERSISTENT = {TILED_ASYNC, TILED_FIXED, TILED_SPLIT, WARP}  # kernels whose CTAs loop over tiles (K3, K4, K6, K5)
+PERSISTENT = {TILED_ASYNC, TILED_FIXED}  # kernels whose CTAs loop over tiles (K3, K4)
 _CAP = 0
 
 
@@ -88,8 +86,6 @@ def test_floodplain_triangles_semi_implicit(kernel, rain):
         op.step_euler(case.dt, 100)
         oracle.step_euler(case.dt, 100)
         assert_state_close(op.get_state(), oracle.array("u_global"), what="floodplain")
-    if kernel == SPLIT224:
-        assert "K6" in op.kernel_info()  # the triangle tiles fit the compiled shape: no fallback
     if kernel == FIXED224:
         assert "K4" in op.kernel_info()
 
@@ -106,8 +102,8 @@ def test_floodplain_hydrostatic_reconstruction(source_method, kernel):
         op.step_euler(case.dt, 100)
         oracle.step_euler(case.dt, 100)
         assert_state_close(op.get_state(), oracle.array("u_global"), what="floodplain HR")
-    if kernel == SPLIT224:
-        assert "K6" in op.kernel_info()
+    if kernel == FIXED224:
+        assert "K4" in op.kernel_info()
     assert (oracle.array("u_global").reshape(-1, 3)[:, 0] < 1e-7).sum() > 1000
 
 
@@ -292,7 +288,7 @@ from golden_cases import GOLDEN as _GOLDEN
 _GOLDEN_NPZ = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden", "swe_golden.npz")
 
 
-@pytest.mark.parametrize("kernel", [GATHER, FIXED224, WARP])
+@pytest.mark.parametrize("kernel", [GATHER, FIXED224, TILED_ASYNC])
 @pytest.mark.parametrize("name", sorted(n for n, v in _GOLDEN.items() if v[1] != "rhs"))
 def test_cuda_path_against_reference_golden_vectors(name, kernel):
     """The CUDA path replays each golden case and is compared with the state the REFERENCE code produced for it."""
