@@ -233,6 +233,22 @@ int rdyb_operator_get_courant_global(RdybOperator op, RdybCourantDiagnostics *di
 /* sum over owned cells of area*h (mass); deterministic two-stage reduction (syncs) */
 int rdyb_operator_get_mass(RdybOperator op, double *mass);
 
+/* Allocation-free mass sum.  NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The reduction of
+ * rdyb_operator_get_mass - sum_i area[i]*h[i] by 1024 fixed blocks and a fixed tree, the partial sums added in index order - with its
+ * scratch (1024 doubles = 8 KiB) in a file-scope `static __device__` array of the library (swe_noalloc.cu) instead of the operator's
+ * cudaMalloc'ed buffer, and the final sum done on the device.
+ *   h, area      DEVICE pointers to num_cells doubles each, on the CURRENT device (e.g. plane 0 of rdyb_operator_device_pointer)
+ *   num_cells    0 .. RDYB_NOALLOC_MAX_CELLS; beyond that RDYB_ERR_ARG_SIZ and nothing is launched
+ *   mass         DEVICE pointer to one double, written by the second kernel
+ *   cuda_stream  cudaStream_t (NULL = the default stream); two kernels are enqueued on it, the call does not synchronise
+ * Calls no cudaMalloc / cudaFree / allocating library routine, copies nothing, never blocks.  Every call on a GPU shares the one static
+ * array (each call overwrites all of it before reading it, so nothing has to be cleared): calls that overlap on the same GPU race -
+ * order them on one stream or with events.  The first call on a device resolves the array's device address (cudaGetSymbolAddress,
+ * cached per device): make that call before a stream capture begins. */
+#define RDYB_NOALLOC_MAX_CELLS 1073741824 /* 2^30 cells */
+int rdyb_mass_sum_noalloc(const double *h, const double *area, int64_t num_cells, double *mass, void *cuda_stream);
+
 /* ---- multi-GPU: NCCL communicator for the halo exchange ---- */
 int rdyb_nccl_unique_id(void *id128 /* 128 bytes out */);
 int rdyb_operator_init_comm(RdybOperator op, int32_t nranks, int32_t rank, const void *id128);

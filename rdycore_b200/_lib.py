@@ -103,6 +103,7 @@ OPERATOR_SYMBOLS = [
     "rdyb_host_alloc", "rdyb_host_free", "rdyb_operator_kernel_info", "rdyb_operator_halo_export", "rdyb_operator_halo_import",
     "rdyb_operator_set_external_source_aos", "rdyb_operator_get_courant_global", "rdyb_operator_set_max_ctas",
     "rdyb_operator_get_wait_cycles", "rdyb_operator_time_set", "rdyb_operator_time_get", "rdyb_operator_advance_device", "rdyb_host_sync_count", "rdyb_operator_enable_bs2002", "rdyb_operator_get_eta_vertices",
+    "rdyb_mass_sum_noalloc",
 ]
 
 _lib = None

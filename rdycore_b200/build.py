@@ -17,7 +17,7 @@ LIB = os.path.join(HERE, "librdyb200.so")
 OBJDIR = os.path.join(HERE, "build")
 
 C_SOURCES = ["rdyb_error.c", "host_mesh.c", "device_layout.c", "petsc_operator_b200.c", "rdy_driver.c", "io_formats.c"]
-CU_SOURCES = ["swe_device.cu"]
+CU_SOURCES = ["swe_device.cu", "swe_noalloc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v", "-Wno-deprecated-gpu-targets",
