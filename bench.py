@@ -51,7 +51,7 @@ def parse_args():
     p.add_argument("--nx", type=int, default=2236, help="quads per side of one GPU's block (cells = 2*nx*ny)")
     p.add_argument("--ny", type=int, default=0)
     p.add_argument("--kernel", default=os.environ.get("RDYB_KERNEL", "auto"), choices=["auto", "gather", "tiled", "async", "fixed"])
-    p.add_argument("--tile", type=int, default=None, help="cells per tile (default: RDYB_TILE, else 224 = K4's shape, 192 with --second-order = K3M's best)")
+    p.add_argument("--tile", type=int, default=None, help="cells per tile (default: RDYB_TILE, else 224 = K4's shape, 192 with --second-order = K4M's shape)")
     p.add_argument("--no-courant", action="store_true", help="skip the per-edge Courant diagnostic (the reference always computes it)")
     p.add_argument("--e2e-steps", type=int, default=10)
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
@@ -501,8 +501,9 @@ def run_b200_arm(args):
     if rank == 0:
         peak, peak_src = measured_peak()
         bytes_per_cell = 140 if args.hr else BYTES_PER_CELL_TRI
-        if args.second_order:  # + gradients written and read (48 + 48) + per-slot LS weights (3 slots x 2 doubles) + face offsets (K1: 3 slots x 4; K2M: 1.5 edges x 4)
-            bytes_per_cell += 96 + 48 + (96 if kernel == GATHER else 48)
+        fused_gradients = args.second_order and "in-kernel gradients" in kinfo  # K4M: no gradient array, no gradient pass
+        if args.second_order:  # + per-slot LS weights (3 slots x 2 doubles) + face offsets (K1: 3 slots x 4; tiles: 1.5 edges x 4) + gradients written and read (48 + 48) unless fused
+            bytes_per_cell += (0 if fused_gradients else 96) + 48 + (96 if kernel == GATHER else 48)
         bytes_per_step_cell = bytes_per_cell
         if args.rk4:  # 4 RHS evaluations + 3 stage AXPYs (read U, K; write Y: 72 B) + the combine (read U, 4 K; write U: 144 B), BASELINE.md §3
             bytes_per_step_cell = 4 * bytes_per_cell + 3 * 72 + 144
@@ -519,7 +520,7 @@ def run_b200_arm(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (traffic * n_owned if traffic else None), "traffic_note": traffic_note, "peak_source": peak_src,
                          "algorithmic_bytes_per_cell": bytes_per_cell, "algorithmic_bytes_per_cell_per_step": bytes_per_step_cell,
-                         "kernel": ("muscl_gradient_kernel + " + ("swe_gather_kernel<RECON>" if kernel == GATHER else "swe_tiled_muscl_async_kernel (K3M)")) if args.second_order else "swe_%s_kernel" % kernel_name,
+                         "kernel": ("muscl_gradient_kernel + " + ("swe_gather_kernel<RECON>" if kernel == GATHER else "swe_tiled_muscl_async_kernel (K3M)")) if args.second_order and not fused_gradients else "swe_tiled_muscl_fixed_kernel (K4M, gradients in-kernel)" if args.second_order else "swe_%s_kernel" % kernel_name,
                          "note": "per-GPU: algorithmic bytes of one step on rank 0 / CUDA-event time per step on the launching stream (max over ranks)"},
             "e2e": e2e,
             "gpu_launches": int(launches),

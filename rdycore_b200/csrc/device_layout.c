@@ -280,8 +280,11 @@ int rdyb_layout_build_muscl(const RdybMeshView *mv, RdybLayout *L) {
       const int32_t other = self == l ? r : l;
       const double dx = mv->cell_xc[r] - mv->cell_xc[l], dy = mv->cell_yc[r] - mv->cell_yc[l];
       const double d = sqrt(dx * dx + dy * dy), w = d > 0.0 ? 1.0 / d : 0.0, wdx = w * dx, wdy = w * dy;
-      L->ell_gcx[q] = inv[4 * self] * wdx + inv[4 * self + 1] * wdy;
-      L->ell_gcy[q] = inv[4 * self + 2] * wdx + inv[4 * self + 3] * wdy;
+      /* the side is folded into the stored weight (an exact sign flip): the left cell sees q_right - q_left = q_nbr - q_self, the right
+       * cell -(q_nbr - q_self), so that the kernels need neither the slot's signed length nor a select */
+      const double sgn = self == l ? 1.0 : -1.0;
+      L->ell_gcx[q] = sgn * (inv[4 * self] * wdx + inv[4 * self + 1] * wdy);
+      L->ell_gcy[q] = sgn * (inv[4 * self + 2] * wdx + inv[4 * self + 3] * wdy);
       L->ell_dxs[q] = mv->edge_xm[e] - mv->cell_xc[self];  L->ell_dys[q] = mv->edge_ym[e] - mv->cell_yc[self];
       L->ell_dxn[q] = mv->edge_xm[e] - mv->cell_xc[other]; L->ell_dyn[q] = mv->edge_ym[e] - mv->cell_yc[other];
     }
@@ -295,7 +298,7 @@ void rdyb_tiled_layout_free(RdybTiledLayout *T) {
   if (!T) return;
   free(T->tile_cell_begin); free(T->halo_offsets); free(T->halo_cells); free(T->edge_offsets); free(T->edge_lr);
   free(T->edge_bidx); free(T->edge_sn); free(T->edge_cn); free(T->edge_len); free(T->cell_edges); free(T->edge_id); free(T->edge_cell); free(T->tile_desc);
-  free(T->edge_off);
+  free(T->edge_off); free(T->halo2_cells); free(T->halo_nbr);
   memset(T, 0, sizeof(*T));
 }
 
@@ -633,5 +636,77 @@ int rdyb_tiled_layout_build_muscl(const RdybLayout *L, RdybTiledLayout *T) {
         T->edge_off[(right ? 0 : 2) * plane + g] = L->ell_dxn[q]; T->edge_off[(right ? 1 : 3) * plane + g] = L->ell_dyn[q];
       }
   }
+  return rdyb_tiled_layout_build_two_ring(L, T);
+}
+
+/* The second ring of every tile and the staged position of each halo cell's neighbours (device_layout.h): what K4M needs to compute the
+ * least-squares gradient of a HALO cell inside the tile kernel with the arithmetic (slot order, weights) of the cell's own tile, so
+ * that both tiles of a shared edge reconstruct bit-identical face values and the scheme stays conservative without a gradient array. */
+int rdyb_tiled_layout_build_two_ring(const RdybLayout *L, RdybTiledLayout *T) {
+  int ierr = RDYB_SUCCESS;
+  int32_t *cand = NULL;
+  int64_t cap2 = 0, n2 = 0;
+  RDYB_CHECK(L && T && T->tile_desc, RDYB_ERR_ARG, "two-ring layout: NULL argument");
+  free(T->halo2_cells); free(T->halo_nbr);
+  T->halo2_cells = NULL; T->halo_nbr = NULL; T->max_halo2 = 0; T->total_halo2 = 0; T->two_ring = 0;
+  const int32_t W = L->width, TC = T->tile_cells, N = L->n_owned;
+  const size_t S = (size_t)L->stride;
+  for (int64_t j = 0; j < T->total_halo; ++j)
+    if (T->halo_cells[j] >= N) return RDYB_SUCCESS; /* a ghost in the first ring: no two-ring staging on this rank */
+  T->halo_nbr = malloc(sizeof(uint16_t) * 4 * (size_t)(T->total_halo > 0 ? T->total_halo : 1));
+  cand = malloc(sizeof(int32_t) * (size_t)RDYB_ELL_WIDTH * (size_t)(T->max_halo > 0 ? T->max_halo : 1));
+  if (!T->halo_nbr || !cand) { ierr = rdyb_fail(RDYB_ERR_MEM, "two-ring layout: out of memory"); goto fail; }
+  memset(T->halo_nbr, 0xff, sizeof(uint16_t) * 4 * (size_t)(T->total_halo > 0 ? T->total_halo : 1));
+  for (int32_t t = 0; t < T->num_tiles; ++t) {
+    int32_t *d = &T->tile_desc[8 * (size_t)t];
+    const int32_t cb = d[0], ce = d[0] + d[1], ho = d[4], nh = d[5];
+    const int32_t *H = T->halo_cells + ho;
+    while (n2 & 3) { GROW(T->halo2_cells, cap2, n2 + 1); T->halo2_cells[n2++] = 0; }
+    /* candidates: neighbours of the halo cells outside tile and halo */
+    int32_t nc = 0;
+    for (int32_t j = 0; j < nh; ++j)
+      for (int32_t k = 0; k < W; ++k) {
+        const int32_t nbr = L->ell_nbr[(size_t)k * S + (size_t)H[j]];
+        if (nbr < 0 || (nbr >= cb && nbr < ce)) continue;
+        const int32_t pos = lower_bound_i32(H, nh, nbr);
+        if (pos < nh && H[pos] == nbr) continue;
+        if (nbr >= N) goto fail; /* a ghost in the second ring: ierr is still RDYB_SUCCESS, the layout simply has no two-ring staging */
+        cand[nc++] = nbr;
+      }
+    qsort(cand, (size_t)nc, sizeof(int32_t), cmp_i32);
+    int32_t nu = 0;
+    for (int32_t j = 0; j < nc; ++j) if (j == 0 || cand[j] != cand[j - 1]) cand[nu++] = cand[j];
+    if (nu > 32766 || TC + nh > 32766) { ierr = rdyb_fail(RDYB_ERR_SUP, "two-ring layout: tile %d stages too many cells for 15-bit positions", t); goto fail; }
+    GROW(T->halo2_cells, cap2, n2 + nu);
+    memcpy(T->halo2_cells + n2, cand, sizeof(int32_t) * (size_t)nu);
+    for (int32_t j = 0; j < nh; ++j)
+      for (int32_t k = 0; k < W; ++k) {
+        const int32_t nbr = L->ell_nbr[(size_t)k * S + (size_t)H[j]];
+        uint16_t v = 0xffffu;
+        if (nbr >= 0) {
+          if (nbr >= cb && nbr < ce) v = (uint16_t)(nbr - cb);
+          else {
+            const int32_t pos = lower_bound_i32(H, nh, nbr);
+            if (pos < nh && H[pos] == nbr) v = (uint16_t)(TC + pos);
+            else v = (uint16_t)(0x8000u | (uint32_t)lower_bound_i32(cand, nu, nbr));
+          }
+        }
+        T->halo_nbr[4 * (size_t)(ho + j) + (size_t)k] = v;
+      }
+    d[6] = (int32_t)n2; d[7] = nu;
+    n2 += nu;
+    if (nu > T->max_halo2) T->max_halo2 = nu;
+    if (n2 > INT32_MAX - 65536) { ierr = rdyb_fail(RDYB_ERR_SUP, "two-ring layout: too many second-ring cells for int32 offsets"); goto fail; }
+  }
+  GROW(T->halo2_cells, cap2, n2 + 16);
+  for (int j = 0; j < 16; ++j) T->halo2_cells[n2 + j] = 0;
+  T->total_halo2 = n2 + 16;
+  T->two_ring = 1;
+  free(cand);
   return RDYB_SUCCESS;
+fail:
+  free(cand);
+  free(T->halo2_cells); free(T->halo_nbr);
+  T->halo2_cells = NULL; T->halo_nbr = NULL; T->max_halo2 = 0; T->two_ring = 0;
+  return ierr;
 }

@@ -44,7 +44,8 @@ typedef struct {
   double  *ell_sn, *ell_cn, *ell_slen;
   int32_t *ell_edge;       /* local edge id of the slot (diagnostics) */
   /* second-order (MUSCL) geometry per ELL slot, built by rdyb_layout_build_muscl (NULL otherwise):
-   *   gcx, gcy : this cell's least-squares gradient weights for the slot's edge, so that grad q += (gcx, gcy) * (q_right - q_left)
+   *   gcx, gcy : this cell's least-squares gradient weights for the slot's edge with the side folded in, so that
+   *              grad q += (gcx, gcy) * (q_neighbour - q_self)   [= w * (q_right - q_left) with w the reference's weight]
    *              (PrecomputeLSGradCoeffs / ComputeLeastSquaresGradients, src/operator_fluxes_ceed.c:884-1038)
    *   dxs, dys : edge midpoint - this cell's centroid;  dxn, dyn : edge midpoint - the neighbour's centroid
    *              (ReconstructFaceValues, src/operator_fluxes_ceed.c:1162-1172) */
@@ -89,6 +90,15 @@ typedef struct {
    * to a multiple of 4, so that a tile's slice of every plane starts 16-byte aligned (bulk copies) */
   double   *edge_off;
   int64_t   edge_off_plane;
+  /* second order, two-ring staging (K4M: the gradients of a tile's cells AND of its halo cells are computed inside the tile kernel):
+   * a tile's SECOND ring = the interior neighbours of its halo cells that are neither tile nor halo cells (sorted, begins padded to 4;
+   * tile_desc[6], [7] = begin, count), and per halo entry the staged position of each of its `width` neighbours in ELL slot order:
+   *   0 .. tile_cells-1 tile cell, tile_cells + k the k-th halo cell, 0x8000 | k the k-th second-ring cell, 0xFFFF no interior neighbour.
+   * two_ring = 0 when a halo cell is a ghost of another rank (its own neighbours are not all here): such layouts exchange gradients. */
+  int32_t  *halo2_cells;
+  uint16_t *halo_nbr;        /* [total_halo][4] */
+  int32_t   max_halo2, two_ring;
+  int64_t   total_halo2;
 } RdybTiledLayout;
 
 int  rdyb_layout_build(const RdybMeshView *mesh, int32_t num_boundaries, const RdybBoundaryView *boundaries, const RdybHaloView *halo,
@@ -98,6 +108,7 @@ void rdyb_layout_free(RdybLayout *layout);
 int  rdyb_tiled_layout_build(const RdybLayout *layout, int32_t tile_cells, RdybTiledLayout *out);
 void rdyb_tiled_layout_free(RdybTiledLayout *tiled);
 int  rdyb_tiled_layout_build_muscl(const RdybLayout *layout, RdybTiledLayout *tiled);
+int  rdyb_tiled_layout_build_two_ring(const RdybLayout *layout, RdybTiledLayout *tiled); /* called by rdyb_tiled_layout_build_muscl */
 
 #ifdef __cplusplus
 }

@@ -24,6 +24,7 @@
 #include "swe_tiled_fixed.cuh"
 #include "swe_tiled_muscl.cuh"
 #include "swe_tiled_muscl_async.cuh"
+#include "swe_tiled_muscl_fixed.cuh"
 
 static std::atomic<int64_t> g_launches{0};
 static std::atomic<int64_t> g_host_syncs{0}; /* host waits for the device (stream / event synchronisations) since load */
@@ -111,6 +112,8 @@ struct RdybOperator_ {
   int recon = 0;
   double *grad = nullptr, *m_gcx = nullptr, *m_gcy = nullptr, *m_dxs = nullptr, *m_dys = nullptr, *m_dxn = nullptr, *m_dyn = nullptr;
   double *t_edge_off = nullptr; /* [4][T.total_edges] face offsets per tile edge: the second-order path on the tiled layout (K2M) */
+  int32_t *t_halo2 = nullptr;   /* two-ring staging of K4M (device_layout.h): second-ring cells per tile ... */
+  uint16_t *t_halo_nbr = nullptr; /* ... and the staged position of every halo cell's neighbours; both NULL when the layout has none */
   bool courant_arg_tiled = false; /* the Courant arg of the last launch is a tile-edge index (else device cell * ELL width + slot) */
   bool ghosts_from_caller = false; /* host-Vec apply: u_local arrives with its ghosts filled (DMGlobalToLocal already ran) */
   /* tiled-kernel device arrays */
@@ -229,7 +232,7 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
                   op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
                   op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y, op->grad, op->m_gcx, op->m_gcy, op->m_dxs, op->m_dys,
-                  op->m_dxn, op->m_dyn, op->t_edge_off};
+                  op->m_dxn, op->m_dyn, op->t_edge_off, op->t_halo2, op->t_halo_nbr};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (void *p : {(void *)op->pipe.order, (void *)op->pipe.local_to_dev, (void *)op->pipe.owned_to_dev, (void *)op->pipe.stage_in, (void *)op->pipe.stage_out})
@@ -399,17 +402,24 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
       tiled_dev_free(&op->td);
       rdyb_tiled_layout_free(&op->T);
       if (op->t_edge_off) { cudaFree(op->t_edge_off); op->t_edge_off = nullptr; }
+      if (op->t_halo2) { cudaFree(op->t_halo2); op->t_halo2 = nullptr; }
+      if (op->t_halo_nbr) { cudaFree(op->t_halo_nbr); op->t_halo_nbr = nullptr; }
       op->has_tiled = false;
       pipe_release(op);
       fpush_release(op);
     }
     if (!op->has_tiled) {
       RDYB_CALL(rdyb_tiled_layout_build(&op->L, tile_cells, &op->T));
+      const bool muscl_tiles = op->recon && !getenv("RDYB_MUSCL_K1"); /* second order on the tiled layout; RDYB_MUSCL_K1 keeps it on K1 */
+      if (muscl_tiles) RDYB_CALL(rdyb_tiled_layout_build_muscl(&op->L, &op->T)); /* BEFORE the upload: it completes the tile descriptors (second ring) */
       RDYB_CALL(tiled_dev_upload(&op->T, &op->L, &op->td));
       RDYB_CALL(ensure_courant_slots(op, op->T.num_tiles + 1));
-      if (op->recon && !getenv("RDYB_MUSCL_K1")) { /* second order on the tiled layout (K2M); RDYB_MUSCL_K1 keeps it on K1 */
-        RDYB_CALL(rdyb_tiled_layout_build_muscl(&op->L, &op->T));
+      if (muscl_tiles) {
         RDYB_CALL(upload(&op->t_edge_off, op->T.edge_off, 4 * (size_t)op->T.edge_off_plane));
+        if (op->T.two_ring) {
+          RDYB_CALL(upload(&op->t_halo2, op->T.halo2_cells, (size_t)op->T.total_halo2));
+          RDYB_CALL(upload(&op->t_halo_nbr, op->T.halo_nbr, 4 * (size_t)op->T.total_halo));
+        }
       }
       op->has_tiled = true;
     }
@@ -653,7 +663,12 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     t.begin = begin; t.end = end;
     if (op->opt_courant) { t.cmax = op->cmax; t.carg = op->carg; } /* one slot per tile */
     op->courant_arg_tiled = true;
-    if (!getenv("RDYB_MUSCL_K2M") && tiled_muscl_async_applicable(op->T, op->t_edge_off)) { /* K3M: 15 % faster than K2M on the B200 (profiles/r2_bench_so_*.json); RDYB_MUSCL_K2M=1 keeps K2M */
+    const int k4m = getenv("RDYB_MUSCL_K2M") ? -1 : tiled_muscl_fixed_mode(op->T, op->t_edge_off, t, op->t_halo2 && op->t_halo_nbr);
+    if (k4m >= 0) { /* K4M: compile-time tile shape; mode 2 computes the gradients inside the kernel (rhs_pass then skips the gradient pass) */
+      op->last_kernel = k4m == 2 ? "swe_tiled_muscl_fixed_kernel (K4M, MUSCL, in-kernel gradients over a two-ring halo)"
+                                 : "swe_tiled_muscl_fixed_kernel (K4M, MUSCL) + muscl_gradient_kernel";
+      RDYB_CALL(tiled_muscl_fixed_launch(op->td, op->T, op->cfg, t, op->t_edge_off, op->t_halo2, op->t_halo_nbr, k4m, euler, op->stream));
+    } else if (!getenv("RDYB_MUSCL_K2M") && tiled_muscl_async_applicable(op->T, op->t_edge_off)) { /* K3M: 15 % faster than K2M on the B200 (profiles/r2_bench_so_*.json); RDYB_MUSCL_K2M=1 keeps K2M */
       op->last_kernel = "swe_tiled_muscl_async_kernel (K3M, MUSCL) + muscl_gradient_kernel";
       RDYB_CALL(tiled_muscl_async_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));
     } else {
@@ -950,6 +965,10 @@ static int rhs_pass(RdybOperator op, double *in, double *out, double dt, bool eu
     if (exchange) { RDYB_CALL(halo_begin(op, in)); RDYB_CALL(halo_end(op)); }
     SweArgs g;
     fill_args(op, g, in, out, dt);
+    /* K4M in mode 2 derives every gradient it needs inside the tile kernel (single-rank layouts only): no gradient pass, no array */
+    const bool in_kernel = op->kernel_kind >= 1 && op->has_tiled && !getenv("RDYB_MUSCL_K2M") && tiled_muscl_applicable(op->T, op->t_edge_off) &&
+                           tiled_muscl_fixed_mode(op->T, op->t_edge_off, g, op->t_halo2 && op->t_halo_nbr) == 2;
+    if (in_kernel) return launch_cells(op, in, out, dt, euler, 0, op->N, 0);
     muscl_gradient_kernel<<<grid_for(op->N, 128), 128, 0, op->stream>>>(g, op->grad, op->N);
     LAUNCHED();
     CU(cudaGetLastError());

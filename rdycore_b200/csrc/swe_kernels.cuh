@@ -128,10 +128,11 @@ __global__ void muscl_gradient_kernel(const SweArgs a, double *__restrict__ grad
     const size_t q = (size_t)k * (size_t)a.stride + (size_t)i;
     const int nbr = a.nbr[q];
     if (nbr < 0) continue; /* empty or boundary slot */
-    const double sgn = a.eslen[q] < 0.0 ? 1.0 : -1.0; /* left cell: q_nbr - q_self; right cell: q_self - q_nbr */
-    const double d0 = sgn * (a.h[nbr] - q0), d1 = sgn * (a.hu[nbr] - q1), d2 = sgn * (a.hv[nbr] - q2);
+    /* the weights carry the side (device_layout.c): left cell +w, right cell -w, both times (q_nbr - q_self).  Explicit FMAs in slot
+     * order: K4M (swe_tiled_muscl_fixed.cuh) repeats exactly this sequence inside the tile kernel */
+    const double d0 = a.h[nbr] - q0, d1 = a.hu[nbr] - q1, d2 = a.hv[nbr] - q2;
     const double cx = a.gcx[q], cy = a.gcy[q];
-    gx0 += cx * d0; gy0 += cy * d0; gx1 += cx * d1; gy1 += cy * d1; gx2 += cx * d2; gy2 += cy * d2;
+    gx0 = fma(cx, d0, gx0); gy0 = fma(cy, d0, gy0); gx1 = fma(cx, d1, gx1); gy1 = fma(cy, d1, gy1); gx2 = fma(cx, d2, gx2); gy2 = fma(cy, d2, gy2);
   }
   const size_t S = (size_t)a.stride;
   grad[i] = gx0; grad[S + i] = gx1; grad[2 * S + i] = gx2; grad[3 * S + i] = gy0; grad[4 * S + i] = gy1; grad[5 * S + i] = gy2;

@@ -29,7 +29,8 @@ class RdybTiledLayout(C.Structure):
                 ("tile_cell_begin", c_i32p), ("tile_desc", c_i32p), ("halo_offsets", c_i32p), ("halo_cells", c_i32p), ("edge_offsets", c_i32p),
                 ("edge_lr", c_u32p), ("edge_bidx", c_i32p), ("edge_id", c_i32p), ("edge_cell", c_i32p),
                 ("edge_sn", c_f64p), ("edge_cn", c_f64p), ("edge_len", c_f64p), ("cell_edges", c_u16p),
-                ("total_edges", C.c_int64), ("total_halo", C.c_int64), ("edge_off", c_f64p), ("edge_off_plane", C.c_int64)]
+                ("total_edges", C.c_int64), ("total_halo", C.c_int64), ("edge_off", c_f64p), ("edge_off_plane", C.c_int64),
+                ("halo2_cells", c_i32p), ("halo_nbr", c_u16p), ("max_halo2", C.c_int32), ("two_ring", C.c_int32), ("total_halo2", C.c_int64)]
 
 
 def _np(ptr, n):
@@ -107,6 +108,60 @@ def test_tile_edge_face_offsets_with_ghosts(monkeypatch):
     halo = case.mesh.halo()
     n_int, n_bnd, nt = _check_offsets(case, 128, halo)
     assert n_int > 0 and n_bnd > 0 and nt > 4
+
+
+@pytest.mark.parametrize("which,tile_cells", [("triangles", 192), ("triangles", 128), ("quads", 192)])
+def test_two_ring_layout_invariants(which, tile_cells):
+    """K4M's two-ring staging (rdyb_tiled_layout_build_two_ring): every interior neighbour of every halo cell of a tile is staged - as a
+    tile cell, a halo cell or a second-ring cell - at the position halo_nbr names, in ELL slot order; the second ring is sorted, disjoint
+    from tile and halo, and its slices are 16-byte aligned."""
+    case = cases.floodplain(nx=44, ny=38, eta0=8.0) if which == "triangles" else cases.dam_break_quads(nx=40, ny=30)
+    view, L, T = _layouts(case, tile_cells)
+    try:
+        assert T.two_ring == 1 and T.max_halo2 > 0
+        S, W, TC = L.stride, L.width, T.tile_cells
+        nbr = _np(L.ell_nbr, 4 * S).reshape(4, S)
+        desc = _np(T.tile_desc, 8 * T.num_tiles).reshape(-1, 8)
+        halo, halo2 = _np(T.halo_cells, T.total_halo), _np(T.halo2_cells, T.total_halo2)
+        hn = _np(T.halo_nbr, 4 * T.total_halo).reshape(-1, 4)
+        worst = 0
+        for cb, ncell, _, _, ho, nh, h2o, nh2 in desc:
+            assert h2o % 4 == 0 and 0 <= nh2 <= T.max_halo2
+            H, H2 = halo[ho:ho + nh], halo2[h2o:h2o + nh2]
+            assert np.all(np.diff(H2) > 0) and not np.intersect1d(H, H2).size and not np.any((H2 >= cb) & (H2 < cb + ncell))
+            used = np.zeros(nh2, bool)
+            for j in range(nh):
+                for k in range(4):
+                    v = int(hn[ho + j, k])
+                    n = int(nbr[k, H[j]]) if k < W else -1
+                    if n < 0:
+                        assert v == 0xFFFF  # boundary or empty slot (RDYB_NO_EDGE is negative too)
+                    elif v & 0x8000:
+                        assert H2[v & 0x7FFF] == n
+                        used[v & 0x7FFF] = True
+                    elif v >= TC:
+                        assert H[v - TC] == n
+                    else:
+                        assert cb + v == n and v < ncell
+            assert used.all()  # nothing is staged in vain
+            worst = max(worst, nh2)
+        assert worst == T.max_halo2
+    finally:
+        lib().rdyb_tiled_layout_free(C.byref(T))
+        lib().rdyb_layout_free(C.byref(L))
+
+
+def test_two_ring_layout_is_off_when_a_halo_cell_is_a_ghost():
+    """On a partitioned mesh the first ring of a frontier tile holds ghosts, whose own neighbours are not all on this rank: no two-ring
+    staging (the gradients of ghosts arrive by halo exchange, K4M runs with the gradient array)."""
+    case = cases.floodplain(nx=44, ny=30, eta0=8.0, px=2, py=1, rank=1)
+    halo = case.mesh.halo()
+    view, L, T = _layouts(case, 192, halo)
+    try:
+        assert T.two_ring == 0 and not T.halo_nbr and not T.halo2_cells
+    finally:
+        lib().rdyb_tiled_layout_free(C.byref(T))
+        lib().rdyb_layout_free(C.byref(L))
 
 
 def test_tiled_muscl_layout_needs_the_slot_geometry():

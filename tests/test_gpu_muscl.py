@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 
 def _tiled_muscl(info: str) -> bool:
     """the second-order path ran on the tiled layout: K3M (bulk-async staged, the default) or K2M (RDYB_MUSCL_K2M=1 / shapes K3M cannot stage)"""
-    return "K3M" in info or "K2M" in info
+    return "K4M" in info or "K3M" in info or "K2M" in info
 LIMITERS = [cases.MUSCL_MINMOD, cases.MUSCL_NONE, cases.MUSCL_VANLEER]
 
 
@@ -164,3 +164,71 @@ def test_async_tiled_second_order(reconstruction, tile, monkeypatch):
     else:
         op.step_euler(case.dt, steps); oracle.step_euler(case.dt, steps)
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order floodplain on K3M")
+
+
+@pytest.mark.parametrize("cap", [0, 3], ids=["fullgrid", "cap3"])
+@pytest.mark.parametrize("consumers", [192, 256])
+@pytest.mark.parametrize("reconstruction", LIMITERS)
+def test_fixed_shape_second_order_k4m(reconstruction, consumers, cap, monkeypatch):
+    """K4M on 192-cell tiles (swe_tiled_muscl_fixed.cuh).  Mode 2 computes the least-squares gradients of tile AND halo cells inside the
+    tile kernel from a two-ring halo with the instruction sequence of muscl_gradient_kernel; mode 0 (RDYB_K4M_GRAD_ARRAY=1) reads the
+    gradient array that kernel writes.  The same gradients bit for bit => the same right-hand side bit for bit.  Against K3M
+    (RDYB_MUSCL_K3M=1) the right-hand side agrees to round-off (K4M takes u, v, sqrt(h) of a face from one MUFU seed); against the oracle
+    the state after 100 steps, with the full grid and with 3 CTAs walking 5 tiles each through both stages."""
+    case = _wet_floodplain(reconstruction)
+    oracle = make_oracle(case)
+    oracle.rhs(case.dt)
+    u_local = oracle.array("u_local").copy()
+    monkeypatch.setenv("RDYB_K4M_CONSUMERS", str(consumers))
+
+    def make(env=None):
+        if env:
+            monkeypatch.setenv(env, "1")
+        op = Operator.from_case(case)
+        op.set_kernel(TILED, 192)
+        op.set_options(courant=True)
+        if cap:
+            op.set_max_ctas(cap)
+        F = op.apply_host(case.dt, u_local)
+        if env:
+            monkeypatch.delenv(env)
+        return op, F
+
+    ref, F_ref = make("RDYB_MUSCL_K3M")
+    arr, F_arr = make("RDYB_K4M_GRAD_ARRAY")
+    op, F = make()
+    assert "K3M" in ref.kernel_info() and "K4M" in arr.kernel_info() and "muscl_gradient_kernel" in arr.kernel_info()
+    assert "K4M" in op.kernel_info() and "in-kernel gradients" in op.kernel_info()
+    assert np.array_equal(F, F_arr)  # in-kernel gradients == the gradient kernel's, bit for bit
+    assert op.courant().max_courant_num == arr.courant().max_courant_num
+    assert (np.abs(F - F_ref) / np.abs(F_ref).max(axis=0)).max() < 1e-13
+    assert op.courant().max_courant_num == pytest.approx(ref.courant().max_courant_num, rel=1e-13)
+    steps = 30 if reconstruction == cases.MUSCL_NONE else 100  # see test_async_tiled_second_order
+    if reconstruction == cases.MUSCL_VANLEER:
+        op.step_rk4(case.dt, steps); oracle.step_rk4(case.dt, steps)
+    else:
+        op.step_euler(case.dt, steps); oracle.step_euler(case.dt, steps)
+    assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order floodplain on K4M")
+    for o in (ref, arr, op):
+        o.close()
+
+
+def test_k4m_conserves_mass_and_repeats_bitwise():
+    """Both tiles of a shared edge reconstruct from bit-identical gradients (each computed in its own stage): with closed walls and no
+    rain the mass is conserved to round-off, and the result does not depend on which CTA ran which tile."""
+    case = _wet_floodplain(cases.MUSCL_MINMOD)
+    case.sources[:] = 0.0
+    runs = []
+    for cap in (0, 3, 0):
+        op = Operator.from_case(case)
+        op.set_kernel(TILED, 192)
+        if cap:
+            op.set_max_ctas(cap)
+        m0 = op.mass()
+        op.step_euler(case.dt, 100)
+        m1 = op.mass()
+        assert "in-kernel gradients" in op.kernel_info()
+        assert abs(m1 - m0) <= 1e-12 * m0 * np.sqrt(100)
+        runs.append(op.get_state())
+        op.close()
+    assert np.array_equal(runs[0], runs[1]) and np.array_equal(runs[0], runs[2])
