@@ -114,6 +114,7 @@ struct RdybOperator_ {
   double *t_edge_off = nullptr; /* [4][T.total_edges] face offsets per tile edge: the second-order path on the tiled layout (K2M) */
   int32_t *t_halo2 = nullptr;   /* two-ring staging of K4M (device_layout.h): second-ring cells per tile ... */
   uint16_t *t_halo_nbr = nullptr; /* ... and the staged position of every halo cell's neighbours; both NULL when the layout has none */
+  double *t_halo_rec = nullptr;   /* [N][8] {1/area, LS weights}: one 64-byte record per cell for K4M's ring-1 gathers (swe_tiled_muscl_fixed.cuh) */
   bool courant_arg_tiled = false; /* the Courant arg of the last launch is a tile-edge index (else device cell * ELL width + slot) */
   bool ghosts_from_caller = false; /* host-Vec apply: u_local arrives with its ghosts filled (DMGlobalToLocal already ran) */
   /* tiled-kernel device arrays */
@@ -232,7 +233,7 @@ extern "C" int rdyb_operator_destroy(RdybOperator *pop) {
                   op->ell_nbr, op->ell_sn, op->ell_cn, op->ell_slen, op->btype, op->bval, op->bflux, op->bacc, op->dev_to_local,
                   op->dev_to_owned, op->send_cells, op->stage, op->stage_idx, op->sendbuf, op->recvbuf, op->cmax, op->carg, op->partial,
                   op->rk_k[0], op->rk_k[1], op->rk_k[2], op->rk_k[3], op->rk_y, op->grad, op->m_gcx, op->m_gcy, op->m_dxs, op->m_dys,
-                  op->m_dxn, op->m_dyn, op->t_edge_off, op->t_halo2, op->t_halo_nbr};
+                  op->m_dxn, op->m_dyn, op->t_edge_off, op->t_halo2, op->t_halo_nbr, op->t_halo_rec};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (void *p : {(void *)op->pipe.order, (void *)op->pipe.local_to_dev, (void *)op->pipe.owned_to_dev, (void *)op->pipe.stage_in, (void *)op->pipe.stage_out})
@@ -404,6 +405,7 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
       if (op->t_edge_off) { cudaFree(op->t_edge_off); op->t_edge_off = nullptr; }
       if (op->t_halo2) { cudaFree(op->t_halo2); op->t_halo2 = nullptr; }
       if (op->t_halo_nbr) { cudaFree(op->t_halo_nbr); op->t_halo_nbr = nullptr; }
+      if (op->t_halo_rec) { cudaFree(op->t_halo_rec); op->t_halo_rec = nullptr; }
       op->has_tiled = false;
       pipe_release(op);
       fpush_release(op);
@@ -419,6 +421,16 @@ extern "C" int rdyb_operator_set_kernel(RdybOperator op, int32_t kind, int32_t t
         if (op->T.two_ring) {
           RDYB_CALL(upload(&op->t_halo2, op->T.halo2_cells, (size_t)op->T.total_halo2));
           RDYB_CALL(upload(&op->t_halo_nbr, op->T.halo_nbr, 4 * (size_t)op->T.total_halo));
+          if (op->L.width == 3) {
+            std::vector<double> rec(8 * (size_t)op->N, 0.0);
+            const size_t S = (size_t)op->L.stride;
+            for (int32_t c = 0; c < op->N; ++c) {
+              double *r = &rec[8 * (size_t)c];
+              r[0] = op->L.inv_area[c];
+              for (int k = 0; k < 3; ++k) { r[1 + k] = op->L.ell_gcx[(size_t)k * S + c]; r[4 + k] = op->L.ell_gcy[(size_t)k * S + c]; }
+            }
+            RDYB_CALL(upload(&op->t_halo_rec, rec.data(), rec.size()));
+          }
         }
       }
       op->has_tiled = true;
@@ -667,7 +679,7 @@ static int launch_cells(RdybOperator op, const double *in, double *out, double d
     if (k4m >= 0) { /* K4M: compile-time tile shape; mode 2 computes the gradients inside the kernel (rhs_pass then skips the gradient pass) */
       op->last_kernel = k4m == 2 ? "swe_tiled_muscl_fixed_kernel (K4M, MUSCL, in-kernel gradients over a two-ring halo)"
                                  : "swe_tiled_muscl_fixed_kernel (K4M, MUSCL) + muscl_gradient_kernel";
-      RDYB_CALL(tiled_muscl_fixed_launch(op->td, op->T, op->cfg, t, op->t_edge_off, op->t_halo2, op->t_halo_nbr, k4m, euler, op->stream));
+      RDYB_CALL(tiled_muscl_fixed_launch(op->td, op->T, op->cfg, t, op->t_edge_off, op->t_halo2, op->t_halo_nbr, op->t_halo_rec, k4m, euler, op->stream));
     } else if (!getenv("RDYB_MUSCL_K2M") && tiled_muscl_async_applicable(op->T, op->t_edge_off)) { /* K3M: 15 % faster than K2M on the B200 (profiles/r2_bench_so_*.json); RDYB_MUSCL_K2M=1 keeps K2M */
       op->last_kernel = "swe_tiled_muscl_async_kernel (K3M, MUSCL) + muscl_gradient_kernel";
       RDYB_CALL(tiled_muscl_async_launch(op->td, op->T, op->cfg, t, op->t_edge_off, euler, op->stream));

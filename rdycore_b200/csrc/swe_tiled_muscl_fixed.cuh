@@ -50,6 +50,10 @@ struct MusclFixedArgs {
   size_t plane;
   const int32_t *__restrict__ halo2_cells;
   const uint16_t *__restrict__ halo_nbr; /* [total_halo][4] */
+  /* [cells][8] {1/area, cx0, cx1, cx2, cy0, cy1, cy2, 0}: what a ring-1 cell needs besides its state, packed into one 64-byte record.
+   * Gathered as seven 8-byte copies they touch 2 sectors of 32 bytes instead of the 7 that the separate planes cost (cp.async.ca: the
+   * copies of one lane after the first hit L1); NULL: read the planes */
+  const double *__restrict__ halo_rec;
   int32_t tile_begin, tile_end;
 };
 
@@ -149,11 +153,17 @@ __global__ void __launch_bounds__(288, 2) swe_tiled_muscl_fixed_kernel(const Mus
           cp_async8(&st.q[0][TC + t], a.h + c);
           cp_async8(&st.q[1][TC + t], a.hu + c);
           cp_async8(&st.q[2][TC + t], a.hv + c);
-          cp_async8(&st.ia[TC + t], a.inv_area + c);
-          if (GM == 2) {
+          if (GM == 2 && q.halo_rec) {
+            const double *rec = q.halo_rec + 8 * (size_t)c;
+            cp_async8(&st.ia[TC + t], rec);
+#pragma unroll
+            for (int j = 0; j < 6; ++j) cp_async8(&st.g[j][TC + t], rec + 1 + j);
+          } else if (GM == 2) {
+            cp_async8(&st.ia[TC + t], a.inv_area + c);
 #pragma unroll
             for (int j = 0; j < 3; ++j) { cp_async8(&st.g[j][TC + t], a.gcx + (size_t)j * Sd + c); cp_async8(&st.g[3 + j][TC + t], a.gcy + (size_t)j * Sd + c); }
           } else {
+            cp_async8(&st.ia[TC + t], a.inv_area + c);
 #pragma unroll
             for (int j = 0; j < 6; ++j) cp_async8(&st.g[j][TC + t], a.grad + (size_t)j * Sd + c);
           }
@@ -377,7 +387,8 @@ static int tiled_muscl_fixed_launch_t(const MusclFixedArgs &q, int ntiles, cudaS
 
 /* all tiles of the rank in one launch; `a.cmax` needs one slot per persistent CTA.  mode from tiled_muscl_fixed_mode (0 or 2) */
 static inline int tiled_muscl_fixed_launch(const TiledDev &d, const RdybTiledLayout &T, const RdybConfig &cfg, const SweArgs &a, const double *edge_off,
-                                           const int32_t *halo2_cells, const uint16_t *halo_nbr, int mode, bool euler, cudaStream_t stream) {
+                                           const int32_t *halo2_cells, const uint16_t *halo_nbr, const double *halo_rec, int mode, bool euler,
+                                           cudaStream_t stream) {
   if (T.num_tiles <= 0) return RDYB_SUCCESS;
   MusclFixedArgs q;
   memset(&q, 0, sizeof(q));
@@ -388,7 +399,7 @@ static inline int tiled_muscl_fixed_launch(const TiledDev &d, const RdybTiledLay
   p.cell_edges = d.cell_edges;
   p.max_cells = T.tile_cells;
   q.edge_off = edge_off; q.plane = (size_t)T.edge_off_plane;
-  q.halo2_cells = halo2_cells; q.halo_nbr = halo_nbr;
+  q.halo2_cells = halo2_cells; q.halo_nbr = halo_nbr; q.halo_rec = getenv("RDYB_K4M_NO_HALO_REC") ? nullptr : halo_rec;
   q.tile_begin = 0; q.tile_end = T.num_tiles;
   const bool xq = cfg.source_method == RDYB_SOURCE_IMPLICIT_XQ2018;
   const int nt = T.num_tiles;
