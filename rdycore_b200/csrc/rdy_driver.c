@@ -375,8 +375,8 @@ PetscErrorCode RDySetup(RDy rdy) {
   }
   RDYB_CALL(rdyb_hostmesh_halo(rdy->mesh, &halo));
   RDYB_CALL(rdyb_operator_create(&rdy->physics, &view, rdy->num_boundaries, rdy->boundaries, halo.num_peers > 0 ? &halo : NULL, rdy->device, NULL, &rdy->op));
-  /* numerics.second_order runs the tiled MUSCL kernel, fastest on 192-cell tiles (K3M, swe_tiled_muscl_async.cuh), unless RDyB200SetKernel chose a shape */
-  if (rdy->physics.reconstruction && rdy->kernel_kind == 3 && rdy->tile_cells == 224) rdy->tile_cells = 192; /* K3M: 0.876 ms against 0.987 (128) and 1.089 (224), profiles/r2_so_tile*.json */
+  /* numerics.second_order runs the tiled MUSCL kernel on 192-cell tiles, the shape K4M is compiled for (swe_tiled_muscl_fixed.cuh), unless RDyB200SetKernel chose a shape */
+  if (rdy->physics.reconstruction && rdy->kernel_kind == 3 && rdy->tile_cells == 224) rdy->tile_cells = 192; /* K4M 0.639 ms; K3M: 0.876 ms against 0.987 (128) and 1.089 (224), profiles/r2_so_tile*.json */
   RDYB_CALL(rdyb_operator_set_kernel(rdy->op, rdy->kernel_kind, rdy->tile_cells));
   RDYB_CALL(rdyb_operator_set_options(rdy->op, 1, 0, 0, 0));
   rdy->time = 0.0; rdy->step = 0;
