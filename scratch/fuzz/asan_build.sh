@@ -9,7 +9,7 @@ for f in rdyb_error host_mesh device_layout petsc_operator_b200 rdy_driver io_fo
   gcc -std=c11 -O1 -g -fsanitize=address,undefined -fno-omit-frame-pointer -fPIC -Iinclude -Irdycore_b200/csrc -I/usr/local/cuda/include \
       -c rdycore_b200/csrc/$f.c -o /tmp/asan/$f.o
 done
-/usr/local/cuda/bin/nvcc -Wno-deprecated-gpu-targets -shared -o /tmp/asan/librdyb200_asan.so /tmp/asan/*.o rdycore_b200/build/swe_device.cu.o -lm -ldl -Xlinker -lasan -Xlinker -lubsan
+/usr/local/cuda/bin/nvcc -Wno-deprecated-gpu-targets -shared -o /tmp/asan/librdyb200_asan.so /tmp/asan/*.o rdycore_b200/build/swe_device.cu.o rdycore_b200/build/swe_noalloc.cu.o -lm -ldl -Xlinker -lasan -Xlinker -lubsan
 export ASAN_OPTIONS=detect_leaks=0:halt_on_error=1:abort_on_error=1 UBSAN_OPTIONS=halt_on_error=1:abort_on_error=1
 export LD_PRELOAD=$(gcc -print-file-name=libasan.so):$(gcc -print-file-name=libubsan.so) RDYB_LIB=/tmp/asan/librdyb200_asan.so
 python -m pytest tests -x -q -m "not gpu" -p no:cacheprovider
