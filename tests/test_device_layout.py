@@ -151,6 +151,78 @@ def test_two_ring_layout_invariants(which, tile_cells):
         lib().rdyb_layout_free(C.byref(L))
 
 
+def test_two_ring_staging_reproduces_the_cell_centric_gradients():
+    """K4M's phase 0 restated in numpy on the layout arrays: per tile, stage tile | ring 1 | ring 2 states, derive the gradient of every
+    tile cell through cell_edges + edge_lr and of every halo cell through halo_nbr, in ELL slot order - and compare with the cell-centric
+    sum of muscl_gradient_kernel (weights with the side folded in, times q_nbr - q_self).  The same products in the same order: equal bits,
+    for every tile that stages a cell.  Also pins the folded weights against the reference's w * (q_right - q_left) form."""
+    case = cases.floodplain(nx=44, ny=38, eta0=8.0)
+    view, L, T = _layouts(case, 192)
+    try:
+        S, W, N, TC = L.stride, L.width, L.n_owned, T.tile_cells
+        assert W == 3
+        nbr = _np(L.ell_nbr, 4 * S).reshape(4, S)
+        gcx, gcy, slen = _np(L.ell_gcx, 4 * S).reshape(4, S), _np(L.ell_gcy, 4 * S).reshape(4, S), _np(L.ell_slen, 4 * S).reshape(4, S)
+        rng = np.random.default_rng(5)
+        q = rng.normal(size=L.n_local)
+
+        def cell_centric(c):
+            gx = gy = 0.0
+            for k in range(W):
+                n = int(nbr[k, c])
+                if n < 0:
+                    continue
+                d = q[n] - q[c]
+                gx, gy = gcx[k, c] * d + gx, gcy[k, c] * d + gy
+            return gx, gy
+
+        # folded weight * (q_nbr - q_self) == unfolded weight * (q_right - q_left): the cell is the left cell iff slen < 0
+        for c in range(0, N, 37):
+            for k in range(W):
+                n = int(nbr[k, c])
+                if n >= 0:
+                    left = slen[k, c] < 0.0
+                    w = gcx[k, c] if left else -gcx[k, c]
+                    assert w * ((q[n] - q[c]) if left else (q[c] - q[n])) == gcx[k, c] * (q[n] - q[c])
+        desc = _np(T.tile_desc, 8 * T.num_tiles).reshape(-1, 8)
+        halo, halo2 = _np(T.halo_cells, T.total_halo), _np(T.halo2_cells, T.total_halo2)
+        hn = _np(T.halo_nbr, 4 * T.total_halo).reshape(-1, 4)
+        lr, ce = _np(T.edge_lr, T.total_edges), _np(T.cell_edges, 4 * S).reshape(4, S)
+        HM = 80
+        for cb, ncell, eo, nedge, ho, nh, h2o, nh2 in desc:
+            staged = np.full(TC + HM + 96, np.nan)
+            staged[:ncell] = q[cb:cb + ncell]
+            staged[TC:TC + nh] = q[halo[ho:ho + nh]]
+            staged[TC + HM:TC + HM + nh2] = q[halo2[h2o:h2o + nh2]]
+            for t in range(ncell):  # tile cells: neighbour = the other endpoint of the slot's tile edge
+                gx = gy = 0.0
+                for k in range(W):
+                    v = int(ce[k, cb + t])
+                    if v == 0xFFFF:
+                        continue
+                    e = int(lr[eo + (v & 0x7FFF)])
+                    if e >> 16 == 0xFFFF:
+                        continue
+                    n = (e & 0xFFFF) if v & 0x8000 else (e >> 16)
+                    d = staged[n] - staged[t]
+                    gx, gy = gcx[k, cb + t] * d + gx, gcy[k, cb + t] * d + gy
+                assert (gx, gy) == cell_centric(cb + t)
+            for j in range(nh):  # ring-1 cells: neighbours at the staged positions halo_nbr names
+                c = int(halo[ho + j])
+                gx = gy = 0.0
+                for k in range(W):
+                    v = int(hn[ho + j, k])
+                    if v == 0xFFFF:
+                        continue
+                    n = TC + HM + (v & 0x7FFF) if v & 0x8000 else v
+                    d = staged[n] - staged[TC + j]
+                    gx, gy = gcx[k, c] * d + gx, gcy[k, c] * d + gy
+                assert not np.isnan(gx) and (gx, gy) == cell_centric(c)
+    finally:
+        lib().rdyb_tiled_layout_free(C.byref(T))
+        lib().rdyb_layout_free(C.byref(L))
+
+
 def test_two_ring_layout_is_off_when_a_halo_cell_is_a_ghost():
     """On a partitioned mesh the first ring of a frontier tile holds ghosts, whose own neighbours are not all on this rank: no two-ring
     staging (the gradients of ghosts arrive by halo exchange, K4M runs with the gradient array)."""
