@@ -232,3 +232,20 @@ def test_k4m_conserves_mass_and_repeats_bitwise():
         runs.append(op.get_state())
         op.close()
     assert np.array_equal(runs[0], runs[1]) and np.array_equal(runs[0], runs[2])
+
+
+@pytest.mark.parametrize("reconstruction", [cases.MUSCL_MINMOD, cases.MUSCL_VANLEER])
+def test_k4m_on_a_small_quad_mesh_uses_the_gradient_array(reconstruction):
+    """Quads have eight least-squares weights per cell, K4M stages six: a quad mesh small enough for K4M's edge capacity (a single
+    192-cell tile holds at most 352 edges) runs it with the gradient array - four cell_edges planes, no halo at all."""
+    case = cases.dam_break_quads(nx=12, ny=12, source_method=cases.SEMI_IMPLICIT)
+    case.config.reconstruction = reconstruction
+    oracle = make_oracle(case)
+    op = Operator.from_case(case)
+    op.set_kernel(TILED, 192)
+    op.step_euler(case.dt, 60)
+    oracle.step_euler(case.dt, 60)
+    info = op.kernel_info()
+    assert "K4M" in info and "muscl_gradient_kernel" in info
+    assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order quads on K4M")
+    op.close()
