@@ -249,3 +249,17 @@ def test_k4m_on_a_small_quad_mesh_uses_the_gradient_array(reconstruction):
     assert "K4M" in info and "muscl_gradient_kernel" in info
     assert_state_close(op.get_state(), oracle.array("u_global"), what="second-order quads on K4M")
     op.close()
+
+
+def test_k4m_single_tile_without_halo():
+    """A triangle mesh that fits one tile: no first ring, no second ring (zero-byte index slices), in-kernel gradients all the same."""
+    case = cases.floodplain(nx=9, ny=8, eta0=40.0)
+    case.config.reconstruction = cases.MUSCL_MINMOD
+    oracle = make_oracle(case)
+    op = Operator.from_case(case)
+    op.set_kernel(TILED, 192)
+    op.step_euler(case.dt, 60)
+    oracle.step_euler(case.dt, 60)
+    assert "in-kernel gradients" in op.kernel_info()
+    assert_state_close(op.get_state(), oracle.array("u_global"), what="second order, one tile")
+    op.close()
